@@ -1,0 +1,394 @@
+#!/usr/bin/env python
+"""Benchmark of the distillation tail: train images/sec + kernel HBM rooflines.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
+
+Contract (one JSON line on rank 0):
+  metric  train images/sec on BASELINE.json's headline config (DKD+DOT ResNet34->ResNet18,
+          synthetic ImageNet 224x224 / 1000 classes, 256 images per GPU), whole job over N GPUs.
+  value   inputs already resident in HBM; K steps between barrier+synchronize, CUDA events,
+          max over ranks.
+  e2e     the same steps through the public call (`trainer.train_iter(batch)`): pinned host batch
+          -> H2D inside the timed region, loss/top-k metrics read back D2H every step.
+  roofline  the DOT update kernel timed live inside the timed region (CUDA events on its stream),
+          algorithmic bytes 32*N_shard per launch vs the measured HBM copy peak.
+  kernels   isolated large-shape sweep of both kernels (L2 flushed between launches).
+  cpu_baseline  the CPU port of the reference path (oracle/) on a bounded sample, host cores.
+`--impl reference` prints the CPU arm alone (rank 0; other ranks exit 0).
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "train_images_per_sec"
+UNIT = "images/s"
+FALLBACK_HBM_GBS = 6650.0
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="imagenet_r34_r18_dkd_dot")
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (0 = the workload's)")
+    ap.add_argument("--cpu-batch", type=int, default=16, help="bounded CPU sample: images per CPU step")
+    ap.add_argument("--no-sweep", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+def hbm_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def profiled_traffic(kernel: str):
+    """dram bytes per launch from the committed ncu capture, if one has been summarised."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(kernel)
+    except Exception:
+        return None
+
+
+# ------------------------------------------------------------------------------- CPU arm
+
+def cpu_arm(workload: str, batch: int, steps: int, warmup: int):
+    """The reference's per-step path restated on CPU (oracle/): backbones forward, dkd/kd + CE loss,
+    two backwards, per-tensor DOT loop -- the same sequence as DOT.train_iter (trainer.py:412-432)."""
+    import oracle
+    from mdistiller_ddp_b200 import workloads as W
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    teacher, student, hw, classes = W.build_pair(workload, seed=0)
+    teacher.eval()
+    student.train()
+    cfg = W.default_cfg(workload)
+    params = [p for _, p in student.named_parameters()]
+    m, d = cfg.SOLVER.SGD.MOMENTUM, cfg.SOLVER.DOT.DELTA
+    opt = oracle.DotListOracle([p.data for p in params], lr=cfg.SOLVER.LR, momentum=m - d, momentum_kd=m + d,
+                               weight_decay=cfg.SOLVER.WEIGHT_DECAY)
+    kind = cfg.DISTILLER.TYPE
+    image, target, _ = W.synthetic_batch(batch, hw, classes, seed=1234)
+
+    def step():
+        zs, _ = student(image)
+        with torch.no_grad():
+            zt, _ = teacher(image)
+        if kind == "DKD":
+            l_ce = cfg.DKD.CE_WEIGHT * oracle.ce_loss(zs, target)
+            l_kd = min(1 / cfg.DKD.WARMUP, 1.0) * oracle.dkd_loss(zs, zt, target, cfg.DKD.ALPHA, cfg.DKD.BETA, cfg.DKD.T)
+        else:
+            l_ce = cfg.KD.LOSS.CE_WEIGHT * oracle.ce_loss(zs, target)
+            l_kd = cfg.KD.LOSS.KD_WEIGHT * oracle.kd_loss(zs, zt, cfg.KD.TEMPERATURE)
+        g_kd = torch.autograd.grad(l_kd, params, retain_graph=True)
+        opt.step_kd(list(g_kd))
+        g_ce = torch.autograd.grad(l_ce, params)
+        opt.step(list(g_ce))
+        return l_kd.item() + l_ce.item()
+
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = time.perf_counter() - t0
+    return {"value": batch * steps / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{steps} steps x {batch} images of {workload} (same nets, 224x224 fp32) on the host CPU, "
+                      f"torch {torch.__version__} intra-op threads={cores}",
+            "ms_per_step": 1e3 * dt / steps}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps, warmup = max(1, min(args.steps, 20)), max(1, min(args.warmup, 3))
+    r = cpu_arm(args.workload, args.cpu_batch, steps, warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": steps, "warmup": warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "per_step_images": args.cpu_batch, "device": "host CPU"},
+        "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------- clocks
+
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), [c.strip() for c in line.split(",")]))
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+
+    def summary(self, t0: float, t1: float):
+        rows = [r for t, r in self.rows if t0 <= t <= t1 and len(r) >= 9] or [r for _, r in self.rows if len(r) >= 9]
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = [float(r[1]) for r in rows]
+        reasons = set()
+        for r in rows:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": float(rows[0][2]), "reasons": sorted(reasons),
+                "samples": len(rows), "power_w_max": max(float(r[3]) for r in rows)}
+
+
+# ------------------------------------------------------------------------------- GPU arm
+
+def kernel_sweep(dev):
+    """Both kernels alone at BASELINE.json's sweep sizes; L2 flushed (256 MB write) between launches."""
+    from mdistiller_ddp_b200 import ops
+    peak, _ = hbm_peak()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    out = {}
+
+    def timed(fn, reps=10):
+        ts = []
+        for i in range(reps + 2):
+            flush.fill_(i & 0xFF)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            b.synchronize()
+            if i >= 2:
+                ts.append(a.elapsed_time(b) * 1e-3)
+        return statistics.median(ts), min(ts)
+
+    for (B, C, kind, T, beta, ce, tag) in (
+            (65536, 1000, ops.LOSS_DKD, 1.0, 0.5, ops.CE_NONE, "dkd_65536x1000"),
+            (65536, 1000, ops.LOSS_DKD, 1.0, 0.5, ops.CE_SPLIT, "dkd+ce_split_65536x1000"),
+            (65536, 1000, ops.LOSS_KD, 1.0, 1.0, ops.CE_NONE, "kd_65536x1000"),
+            (16384, 1000, ops.LOSS_DKD, 1.0, 0.5, ops.CE_NONE, "dkd_16384x1000"),
+            (65536, 100, ops.LOSS_DKD, 4.0, 8.0, ops.CE_NONE, "dkd_65536x100"),
+            (65536, 100, ops.LOSS_DKD, 4.0, 8.0, ops.CE_SPLIT, "dkd+ce_split_65536x100_T4"),
+            (256, 1000, ops.LOSS_DKD, 1.0, 0.5, ops.CE_SPLIT, "dkd+ce_split_256x1000"),
+            (64, 100, ops.LOSS_DKD, 4.0, 8.0, ops.CE_SPLIT, "dkd+ce_split_64x100_T4")):
+        zs = torch.randn(B, C, device=dev) * 3
+        zt = torch.randn(B, C, device=dev) * 3
+        y = torch.randint(0, C, (B,), device=dev)
+        gk, gc, lo = torch.empty_like(zs), torch.empty_like(zs), torch.empty(2, device=dev)
+        med, best = timed(lambda: ops.distill_loss(zs, zt, y, kind=kind, alpha=1.0, beta=beta, temperature=T,
+                                                   ce_mode=ce, grad_kd=gk, grad_ce=gc, loss_out=lo))
+        nbytes = (16 if ce == ops.CE_SPLIT else 12) * B * C + 8 * B + 8
+        out[tag] = {"us": med * 1e6, "GB/s": nbytes / med / 1e9, "frac_of_measured_peak": nbytes / med / 1e9 / peak,
+                    "frac_of_8TBs": nbytes / med / 8e12, "bytes": nbytes}
+        del zs, zt, gk, gc
+    for n, tag in ((11_689_512, "dot_resnet18_11.7M"), (25_557_032, "dot_resnet50_25.6M")):
+        p, gt, gk2 = (torch.randn(n, device=dev) * 0.1 for _ in range(3))
+        vt, vk = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+        med, best = timed(lambda: ops.dot_step(p, gt, gk2, vt, vk, lr=0.2, momentum=0.81, momentum_kd=0.99,
+                                               weight_decay=1e-4))
+        out[tag] = {"us": med * 1e6, "GB/s": 32 * n / med / 1e9, "frac_of_measured_peak": 32 * n / med / 1e9 / peak,
+                    "frac_of_8TBs": 32 * n / med / 8e12, "bytes": 32 * n}
+        med, best = timed(lambda: ops.sgd_step(p, gt, vt, lr=0.05, momentum=0.9, weight_decay=5e-4))
+        out[tag.replace("dot_", "sgd_")] = {"us": med * 1e6, "GB/s": 20 * n / med / 1e9,
+                                            "frac_of_measured_peak": 20 * n / med / 1e9 / peak, "bytes": 20 * n}
+    return out
+
+
+def run_b200_arm(args):
+    import torch.distributed as dist
+    import mdistiller_ddp_b200 as b200
+    from mdistiller_ddp_b200 import ops, workloads as W
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    torch.backends.cudnn.benchmark = True          # as tools/train.py:9
+
+    per_gpu = args.batch or W.WORKLOADS[args.workload][7]
+    teacher, student, hw, classes = W.build_pair(args.workload, seed=0)
+    cfg = W.default_cfg(args.workload)
+    distiller = b200.distiller_dict[cfg.DISTILLER.TYPE](student, teacher, cfg).to(dev).train()
+    trainer = b200.StandaloneTrainer(distiller, cfg)
+    n_params = sum(p.numel() for p in distiller.get_learnable_parameters())
+    shard_elems = trainer.optimizer._space.shard_len
+
+    host = W.synthetic_batch(per_gpu, hw, classes, seed=1234 + rank, pin=True)
+    resident = tuple(t.to(dev) for t in host)
+    epoch = 1
+
+    # live timing of our two kernels inside the timed region (events on the launching stream)
+    probes = {"dot": [], "loss": []}
+    probing = {"on": False}
+    orig_dot, orig_loss = ops.dot_step, ops.distill_loss
+
+    def wrap(name, fn):
+        def inner(*a, **k):
+            if not probing["on"]:
+                return fn(*a, **k)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            r = fn(*a, **k)
+            e1.record()
+            probes[name].append((e0, e1))
+            return r
+        return inner
+
+    ops.dot_step = wrap("dot", orig_dot)
+    ops.distill_loss = wrap("loss", orig_loss)
+    # losses.py / optim.py call through the `ops` module attribute, so the wrappers are seen
+
+    def barrier():
+        if world > 1:
+            dist.barrier(device_ids=[local])
+        torch.cuda.synchronize()
+
+    def device_step():
+        return trainer.tail_step(resident[0], resident[1], epoch)
+
+    for _ in range(max(args.warmup, 3)):
+        device_step()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    time.sleep(0.3)
+    probing["on"] = True
+    launches0 = ops.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t_wall0 = time.perf_counter()
+    e0.record()
+    for _ in range(args.steps):
+        device_step()
+    e1.record()
+    barrier()
+    t_wall1 = time.perf_counter()
+    probing["on"] = False
+    launches = ops.launch_count - launches0
+    secs = e0.elapsed_time(e1) * 1e-3
+    clocks = sampler.summary(t_wall0, t_wall1)
+
+    # end-to-end: public call with host (pinned) batch, H2D + metrics D2H inside the timed region
+    meters = b200.new_train_meters()
+    for _ in range(2):
+        trainer.train_iter(host, epoch, meters)
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    for _ in range(args.steps):
+        trainer.train_iter(host, epoch, meters)
+    f1.record()
+    barrier()
+    sampler.stop()
+    e2e_secs = f0.elapsed_time(f1) * 1e-3
+
+    t = torch.tensor([secs, e2e_secs], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    secs, e2e_secs = t.tolist()
+
+    dot_t = [a.elapsed_time(b) * 1e-3 for a, b in probes["dot"]]
+    loss_t = [a.elapsed_time(b) * 1e-3 for a, b in probes["loss"]]
+    peak, peak_src = hbm_peak()
+    dot_avg = sum(dot_t) / len(dot_t)
+    dot_bytes = 32 * shard_elems
+    loss_avg = sum(loss_t) / len(loss_t)
+    loss_bytes = 16 * per_gpu * classes + 8 * per_gpu + 8
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    h2d = sum(t.numel() * t.element_size() for t in host[:2])
+    line = {
+        "metric": METRIC, "value": world * per_gpu * args.steps / secs, "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * secs / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: DKD+DOT ResNet34->ResNet18, synthetic ImageNet 224x224x3, "
+                               f"1000 classes, random-init" if args.workload == "imagenet_r34_r18_dkd_dot" else args.workload,
+                   "per_gpu_batch": per_gpu, "global_batch": per_gpu * world, "student_params": n_params,
+                   "parallelism": f"dp{world}: reduce-scatter x2 -> DOT on 1/{world} shard -> all-gather",
+                   "backbone_math": "fp32 storage, cuDNN TF32 convolutions allowed (torch default, as the reference)",
+                   "l2": "inputs_exceed_l2 (154 MB batch, >1 GB activations per step)"},
+        "e2e": {"value": world * per_gpu * args.steps / e2e_secs, "unit": UNIT, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": 20, "ms_per_step": 1e3 * e2e_secs / args.steps,
+                "api": "StandaloneTrainer.train_iter((image, target, index), epoch, meters) -- the mirror of "
+                       "DOT.train_iter (trainer.py:412-461)"},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "roofline": {"kernel": "flat_step_vec4<true,true> (mdb200_dot_step)", "bound": "hbm",
+                     "achieved": dot_bytes / dot_avg / 1e9, "peak": peak, "unit": "GB/s",
+                     "frac": dot_bytes / dot_avg / 1e9 / peak, "traffic": profiled_traffic("dot_step"),
+                     "peak_source": peak_src, "bytes_per_launch": dot_bytes, "us_per_launch": dot_avg * 1e6,
+                     "launches_timed": len(dot_t),
+                     "note": "timed in-step right after backward: part of the 234 MB working set is L2-resident"},
+        "loss_kernel_in_step": {"kernel": "loss_rows_in_registers (mdb200_distill_loss)", "us_per_launch": loss_avg * 1e6,
+                                "bytes_per_launch": loss_bytes, "GB/s": loss_bytes / loss_avg / 1e9,
+                                "note": "256x1000 is 4 MB: launch-latency bound, see kernels{} for the large-shape sweep"},
+    }
+    if not args.no_sweep:
+        line["kernels"] = kernel_sweep(dev)
+    if world == 1 and not args.no_cpu:
+        line["cpu_baseline"] = {k: v for k, v in cpu_arm(args.workload, args.cpu_batch, 8, 1).items()
+                                if k != "ms_per_step"}
+    else:
+        line["cpu_baseline"] = None
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_b200_arm(args)
+
+
+if __name__ == "__main__":
+    main()

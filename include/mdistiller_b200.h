@@ -1,0 +1,137 @@
+/*
+ * mdistiller_b200 -- C-ABI of the B200 (sm_100a) distillation tail.
+ *
+ * One shared library, plain C linkage, raw device pointers + sizes + an explicit
+ * stream.  No entry point below allocates, frees or retains device memory: every
+ * buffer, the reduction workspace included, belongs to the caller and must stay
+ * alive until the work queued on `stream` has finished.  Calls return 0 on
+ * success, a negative MDB200_E* code for a rejected argument, or a positive
+ * cudaError_t when the launch failed; nothing is thrown across the boundary.
+ *
+ * The reference (youngyoonii/mdistiller-ddp) has no native layer; each entry point
+ * cites the Python it replaces (paths relative to the reference root).
+ */
+#ifndef MDISTILLER_B200_H_
+#define MDISTILLER_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MDB200_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define MDB200_API __attribute__((visibility("default")))
+#else
+#define MDB200_API
+#endif
+
+/* argument errors (negative so they never collide with cudaError_t) */
+#define MDB200_EINVAL   (-1)   /* null pointer, non-positive size, bad mode/flag      */
+#define MDB200_ESHAPE   (-2)   /* leading dimension smaller than the row length      */
+#define MDB200_EWORKSPC (-3)   /* workspace missing or smaller than required         */
+#define MDB200_EALIGN   (-4)   /* pointer not 4-byte aligned                         */
+
+/* loss kinds */
+#define MDB200_LOSS_DKD 0      /* alpha*TCKD + beta*NCKD   (distillers/DKD.py:8-32)  */
+#define MDB200_LOSS_KD  1      /* T^2 * KL(p_t || p_s)     (distillers/KD.py:8-13)   */
+
+/* cross-entropy handling of mdb200_distill_loss */
+#define MDB200_CE_NONE     0   /* distillation term only                              */
+#define MDB200_CE_SPLIT    1   /* CE gradient written to its own buffer (DOT trainer) */
+#define MDB200_CE_COMBINED 2   /* CE gradient added into grad_kd (base trainer)       */
+
+/* membership of a parameter range in DOT's two gradient lists (engine/dot.py:36-39,49-54) */
+#define MDB200_DOT_BOTH      0 /* has task and KD gradient: m_task / m_kd             */
+#define MDB200_DOT_TASK_ONLY 1 /* task gradient only: coefficient (m_task+m_kd)/2     */
+#define MDB200_DOT_KD_ONLY   2 /* KD gradient only: weight decay joins the KD branch  */
+
+MDB200_API int mdb200_abi_version(void);
+
+/* Human-readable text for a code returned by any entry point (static storage). */
+MDB200_API const char *mdb200_error_string(int code);
+
+/* Bytes of device workspace mdb200_distill_loss needs (a constant; 256-byte
+ * aligned buffer).  The first 64 bytes must be zero before the FIRST call; the
+ * kernel leaves them zero again, so one memset at allocation time is enough.
+ * Concurrent launches on different streams need different workspaces. */
+MDB200_API size_t mdb200_loss_workspace_bytes(void);
+
+/*
+ * Fused logit loss: value AND gradient w.r.t. the student logits in one pass.
+ *
+ * Replaces dkd_loss (+ _get_gt_mask/_get_other_mask/cat_mask) at
+ * mdistiller/distillers/DKD.py:8-51, kd_loss at mdistiller/distillers/KD.py:8-13,
+ * the F.cross_entropy term at DKD.py:71 / KD.py:31 and the autograd backward of all
+ * three.
+ *
+ *   z_student, z_teacher  [rows, classes] fp32, row stride ld_s / ld_t elements
+ *   target                [rows] int64 class indices in [0, classes)
+ *   kind                  MDB200_LOSS_DKD | MDB200_LOSS_KD (alpha, beta ignored for KD)
+ *   kd_scale              outer factor on the distillation term: warm-up
+ *                         min(epoch/WARMUP,1) (DKD.py:72) or KD_WEIGHT (KD.py:32)
+ *   ce_mode, ce_scale     CE_WEIGHT * F.cross_entropy(z_student, target) handling
+ *   grad_kd               [rows, classes] fp32 out, row stride ld_g:
+ *                         d(kd_scale*loss_kd)/dz_student (+ CE part if CE_COMBINED)
+ *   grad_ce               same shape/stride, written only for CE_SPLIT (else may be NULL)
+ *   loss_out              2 floats on the device: {kd_scale*loss_kd, ce_scale*loss_ce}
+ *                         (second is 0 for CE_NONE)
+ *   workspace             see mdb200_loss_workspace_bytes
+ *
+ * The means are over `rows` (the per-rank batch), exactly like the reference.
+ * Rows are reduced in a fixed order: results are bit-reproducible run to run.
+ */
+MDB200_API int mdb200_distill_loss(const float *z_student, const float *z_teacher, const int64_t *target,
+                        int64_t rows, int64_t classes, int64_t ld_s, int64_t ld_t,
+                        int kind, float alpha, float beta, float temperature,
+                        float kd_scale, int ce_mode, float ce_scale,
+                        float *grad_kd, float *grad_ce, int64_t ld_g,
+                        float *loss_out, void *workspace, size_t workspace_bytes,
+                        void *stream);
+
+/*
+ * out[i] = grad[i] * (*upstream)   -- the autograd "grad_output" multiply
+ * (what torch does behind loss.backward() for DKD.py:72 / KD.py:32), with the
+ * scalar read on the device so the host never synchronises.  out may alias grad.
+ */
+MDB200_API int mdb200_scale_by_device_scalar(float *out, const float *grad, const float *upstream,
+                                  int64_t n, void *stream);
+
+/*
+ * Distillation-Oriented Trainer update on flat fp32 ranges, in place.
+ *
+ * Replaces dot() at mdistiller/engine/dot.py:15-55 as driven by
+ * DistillationOrientedTrainer.step_kd/step (dot.py:96-174): per element
+ *   d   = grad_scale*g_task + wd*p;  v_task = first_task ? d : m_task*v_task + (1-damp)*d
+ *   p  -= lr*v_task                  (v_task bypassed when momentum == 0, dot.py:31,40)
+ *   v_kd = first_kd ? gk : m_kd*v_kd + (1-damp)*gk,  gk = grad_scale*g_kd
+ *   p  -= lr*v_kd
+ * `membership` selects the reference's coefficient/decay rules for ranges that are
+ * in only one gradient list; the buffers of the absent branch may be NULL.
+ * grad_scale = 1/world_size after a sum reduce-scatter, 1 otherwise.
+ * 32 algorithmic bytes per element (BOTH), n elements, any alignment >= 4 bytes
+ * (16-byte aligned pointers take the vector path).
+ */
+MDB200_API int mdb200_dot_step(float *p, const float *g_task, const float *g_kd,
+                    float *v_task, float *v_kd, int64_t n,
+                    float lr, float momentum, float momentum_kd, float weight_decay,
+                    float dampening, float grad_scale, int first_task, int first_kd,
+                    int membership, void *stream);
+
+/*
+ * Single-momentum SGD on a flat range, in place: torch.optim.SGD(momentum,
+ * weight_decay, dampening, nesterov=False) as built by BaseTrainer.init_optimizer
+ * (mdistiller/engine/trainer.py:86-91) and stepped at trainer.py:321.
+ * v may be NULL when momentum == 0.  20 algorithmic bytes per element.
+ */
+MDB200_API int mdb200_sgd_step(float *p, const float *g, float *v, int64_t n,
+                    float lr, float momentum, float weight_decay, float dampening,
+                    float grad_scale, int first_step, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MDISTILLER_B200_H_ */

@@ -1,0 +1,525 @@
+// Fused DKD / KD (+ cross-entropy) logit loss: value and d/dz_student in one pass.
+//
+// Replaces mdistiller/distillers/DKD.py:8-51, KD.py:8-13, the F.cross_entropy term at
+// DKD.py:71 / KD.py:31 and their autograd backward.  Mathematics:
+// SURVEY.md Appendix A.1/A.2.
+//
+// Shape of the computation (bandwidth bound, no tensor cores): every row of the two
+// [rows, classes] logit matrices is read ONCE with 128-bit streaming loads into
+// registers, reduced with warp shuffles inside a group of LPR lanes, and the gradient
+// row is written once.  12 algorithmic bytes per element (16 with a split CE gradient).
+//
+// Per row, with u = z/T and g the label:
+//   m  = max_{j != g} u_j                      (label excluded for DKD, included for KD)
+//   e_j = exp(u_j - m),  E = sum e_j           (for student and teacher)
+//   W  = sum et_j * ((ut_j - mt) - (us_j - ms))
+//   KL over the kept classes = W/Et - (log Et - log Es)           -> NCKD (DKD) / KL (KD)
+//   pi = exp(u_g - m) / (exp(u_g - m) + E)                        -> TCKD from log-space terms
+// The label term and the rest are accumulated separately, which is what the reference's
+// cat_mask does and what keeps (1 - pi) accurate for confident rows (Appendix A.4).
+// Everything stays finite where the reference's torch.log(0) would give inf/nan.
+
+#include "common.cuh"
+
+namespace mdb200 {
+
+constexpr int kLossThreads = 256;
+constexpr int kLossWarps = kLossThreads / 32;
+constexpr int kMaxCtas = 2048;             // partial-sum slots per loss term in the workspace
+constexpr size_t kWorkspaceHeader = 64;    // ticket counter lives here, zero between launches
+constexpr float kNegBig = -1.0e30f;        // padding / masked label: exp2 -> 0, differences stay finite
+
+struct LossArgs {
+    const float *zs, *zt;
+    const long long *target;
+    float *gkd, *gce;
+    long long rows, classes, ld_s, ld_t, ld_g;
+    float alpha, beta, inv_t, k2;  // k2 = log2(e) / T
+    float c_kd;                    // kd_scale * T / rows      (gradient prefactor)
+    float c_ce;                    // ce_scale / rows
+    double l_kd;                   // kd_scale * T^2 / rows    (loss prefactor)
+    double l_ce;                   // ce_scale / rows
+    double *part;                  // [2][kMaxCtas] per-CTA partial sums
+    unsigned *ticket;
+    float *loss_out;
+};
+
+struct RowCoef {
+    float cs, ct;      // grad_kd_j = cs*es_j - ct*et_j           (kept classes)
+    float gt_kd;       // added at the label column
+    float cce, gt_ce;  // grad_ce_j = cce*e_j (+ gt_ce at the label)
+    float loss_kd, loss_ce;
+};
+
+// Row-level scalar algebra shared by the register-resident and the generic kernel.
+//   CE: 0 = none, 1 = T == 1 (softmax(z_s) falls out of the student terms), 2 = any T.
+template <bool DKD, int CE>
+__device__ __forceinline__ RowCoef row_coefficients(const LossArgs &A, float ms, float mt, float Es,
+                                                    float Et, float W, float zsg, float ztg, float m1,
+                                                    float Z1) {
+    RowCoef r;
+    r.cce = r.gt_ce = r.loss_ce = 0.f;
+    const float logEs = logf(Es), logEt = logf(Et);
+    const float kl_kept = W * A.inv_t / Et - (logEt - logEs);
+    if (DKD) {
+        const float dgs = (zsg - ms) * A.inv_t, dgt = (ztg - mt) * A.inv_t;
+        const float hs = fmaxf(dgs, 0.f), ht = fmaxf(dgt, 0.f);
+        const float shs = __expf(-hs), sht = __expf(-ht);
+        const float as = __expf(dgs - hs), bs = Es * shs;
+        const float at = __expf(dgt - ht), bt = Et * sht;
+        const float Zs = as + bs, Zt = at + bt;
+        const float logZs = logf(Zs), logZt = logf(Zt);
+        const float lpi_s = (dgs - hs) - logZs, lpi_t = (dgt - ht) - logZt;    // log pi
+        const float lom_s = (logEs - hs) - logZs, lom_t = (logEt - ht) - logZt;  // log (1 - pi)
+        const float pi_s = as / Zs, pi_t = at / Zt;
+        const float om_s = bs / Zs, om_t = bt / Zt;
+        const float tckd = pi_t * (lpi_t - lpi_s) + om_t * (lom_t - lom_s);
+        r.loss_kd = A.alpha * tckd + A.beta * kl_kept;
+        const float d = (pi_s > 0.5f) ? (om_t - om_s) : (pi_s - pi_t);  // pi_s - pi_t without cancellation
+        r.cs = A.c_kd * (A.beta - A.alpha * d) / Es;
+        r.ct = A.c_kd * A.beta / Et;
+        r.gt_kd = A.c_kd * A.alpha * d;
+        if (CE == 1) {
+            r.cce = A.c_ce * shs / Zs;
+            r.gt_ce = -A.c_ce * om_s;
+            r.loss_ce = -lpi_s;
+        }
+    } else {
+        r.loss_kd = kl_kept;
+        r.cs = A.c_kd / Es;
+        r.ct = A.c_kd / Et;
+        r.gt_kd = 0.f;
+        if (CE == 1) {
+            r.cce = A.c_ce / Es;
+            r.gt_ce = -A.c_ce;
+            r.loss_ce = logEs - (zsg - ms);
+        }
+    }
+    if (CE == 2) {
+        const float e1g = __expf(zsg - m1);
+        const float Zf = DKD ? Z1 + e1g : Z1;  // DKD masked the label out of the register row
+        r.cce = A.c_ce / Zf;
+        r.gt_ce = DKD ? -A.c_ce * (Z1 / Zf) : -A.c_ce;
+        r.loss_ce = logf(Zf) - (zsg - m1);
+    }
+    return r;
+}
+
+template <int W>
+__device__ __forceinline__ float group_max(float v) {
+#pragma unroll
+    for (int o = W / 2; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+template <int W>
+__device__ __forceinline__ float group_sum(float v) {
+#pragma unroll
+    for (int o = W / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// CTA partials -> workspace; the last CTA to arrive adds them in index order, so the
+// two loss values are reproducible bit for bit (fixed grid => fixed summation tree).
+__device__ __forceinline__ void publish_loss(const LossArgs &A, double cta_kd, double cta_ce) {
+    __shared__ bool is_last;
+    if (threadIdx.x == 0) {
+        A.part[blockIdx.x] = cta_kd;
+        A.part[kMaxCtas + blockIdx.x] = cta_ce;
+        __threadfence();
+        const unsigned t = atomicAdd(A.ticket, 1u);
+        is_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!is_last || threadIdx.x >= 32) return;
+    __threadfence();
+    double s_kd = 0.0, s_ce = 0.0;
+    for (unsigned i = threadIdx.x; i < gridDim.x; i += 32) {
+        s_kd += __ldcg(A.part + i);
+        s_ce += __ldcg(A.part + kMaxCtas + i);
+    }
+    s_kd = warp_sum(s_kd);
+    s_ce = warp_sum(s_ce);
+    if (threadIdx.x == 0) {
+        A.loss_out[0] = (float)(s_kd * A.l_kd);
+        A.loss_out[1] = (float)(s_ce * A.l_ce);
+        *A.ticket = 0u;  // ready for the next launch on this workspace
+    }
+}
+
+__device__ __forceinline__ void cta_reduce_and_publish(const LossArgs &A, double acc_kd, double acc_ce) {
+    __shared__ double sh[2][kLossWarps];
+    acc_kd = warp_sum(acc_kd);
+    acc_ce = warp_sum(acc_ce);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+        sh[0][warp] = acc_kd;
+        sh[1][warp] = acc_ce;
+    }
+    __syncthreads();
+    double cta_kd = 0.0, cta_ce = 0.0;
+    if (threadIdx.x == 0) {
+        const int nw = blockDim.x >> 5;
+        for (int w = 0; w < nw; ++w) {
+            cta_kd += sh[0][w];
+            cta_ce += sh[1][w];
+        }
+    }
+    publish_loss(A, cta_kd, cta_ce);
+}
+
+#define MDB200_FOR4(V, BODY) \
+    { float &x = V.x; BODY } { float &x = V.y; BODY } { float &x = V.z; BODY } { float &x = V.w; BODY }
+
+// ---------------------------------------------------------------------------------------
+// Register-resident kernel: a group of LPR lanes owns one row, NV float4 per lane per matrix.
+// Requires classes % 4 == 0, 16-byte aligned rows, classes <= LPR*NV*4.
+// ---------------------------------------------------------------------------------------
+template <int LPR, int NV, bool DKD, int CE, bool SPLIT>
+__global__ void __launch_bounds__(kLossThreads) loss_rows_in_registers(const LossArgs A) {
+    constexpr int GPW = 32 / LPR;  // rows per warp
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sub = lane % LPR, grp = lane / LPR;
+    const int nvec = (int)(A.classes >> 2);
+    const long long sweep = (long long)gridDim.x * kLossWarps * GPW;
+    double acc_kd = 0.0, acc_ce = 0.0;
+
+    for (long long base = ((long long)blockIdx.x * kLossWarps + warp) * GPW; base < A.rows; base += sweep) {
+        const long long row = base + grp;
+        const bool live = row < A.rows;           // idle groups of the last warp redo the last row
+        const long long r = live ? row : A.rows - 1;
+        const float4 *ps = reinterpret_cast<const float4 *>(A.zs + r * A.ld_s);
+        const float4 *pt = reinterpret_cast<const float4 *>(A.zt + r * A.ld_t);
+
+        float4 s[NV], t[NV];
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int v = sub + i * LPR;
+            if (v < nvec) {
+                s[i] = ld_stream(ps + v);
+                t[i] = ld_stream(pt + v);
+            } else {
+                s[i] = t[i] = make_float4(kNegBig, kNegBig, kNegBig, kNegBig);
+            }
+        }
+
+        // label logits: picked up (and, for DKD, masked out of the row) by the owning lane
+        float zsg = kNegBig, ztg = kNegBig;
+        int gv = -1, gc = 0;
+        if (DKD || CE != 0) {
+            const long long g = A.target[r];
+            const bool ok = g >= 0 && g < A.classes;
+            gv = ok ? (int)(g >> 2) : -1;
+            gc = (int)(g & 3);
+#pragma unroll
+            for (int i = 0; i < NV; ++i) {
+                if (sub + i * LPR == gv) {
+                    if (gc == 0) { zsg = s[i].x; ztg = t[i].x; if (DKD) s[i].x = t[i].x = kNegBig; }
+                    else if (gc == 1) { zsg = s[i].y; ztg = t[i].y; if (DKD) s[i].y = t[i].y = kNegBig; }
+                    else if (gc == 2) { zsg = s[i].z; ztg = t[i].z; if (DKD) s[i].z = t[i].z = kNegBig; }
+                    else { zsg = s[i].w; ztg = t[i].w; if (DKD) s[i].w = t[i].w = kNegBig; }
+                }
+            }
+            const int owner = ok ? (gv % LPR) : 0;
+            zsg = __shfl_sync(0xffffffffu, zsg, owner, LPR);
+            ztg = __shfl_sync(0xffffffffu, ztg, owner, LPR);
+        }
+
+        // pass 1: maxima of the kept classes
+        float ms = kNegBig, mt = kNegBig;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            ms = fmaxf(ms, fmaxf(fmaxf(s[i].x, s[i].y), fmaxf(s[i].z, s[i].w)));
+            mt = fmaxf(mt, fmaxf(fmaxf(t[i].x, t[i].y), fmaxf(t[i].z, t[i].w)));
+        }
+        ms = group_max<LPR>(ms);
+        mt = group_max<LPR>(mt);
+        const float m1 = fmaxf(ms, zsg);  // T = 1 row maximum for the general CE
+
+        // pass 2: exponentials replace the logits in place; sums and the cross term
+        float Es = 0.f, Et = 0.f, W = 0.f, Z1 = 0.f;
+        float4 c1[CE == 2 ? NV : 1];
+        constexpr float kLog2e = 1.4426950408889634f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            float4 e1 = make_float4(0.f, 0.f, 0.f, 0.f);
+#define MDB200_P2(c)                                                   \
+    {                                                                  \
+        const float ds = s[i].c - ms, dt = t[i].c - mt;                \
+        if (CE == 2) { e1.c = ex2_approx((s[i].c - m1) * kLog2e); Z1 += e1.c; } \
+        const float es = ex2_approx(ds * A.k2), et = ex2_approx(dt * A.k2);     \
+        Es += es; Et += et;                                            \
+        W = fmaf(et, dt - ds, W);                                      \
+        s[i].c = es; t[i].c = et;                                      \
+    }
+            MDB200_P2(x) MDB200_P2(y) MDB200_P2(z) MDB200_P2(w)
+#undef MDB200_P2
+            if (CE == 2) c1[i] = e1;
+        }
+        Es = group_sum<LPR>(Es);
+        Et = group_sum<LPR>(Et);
+        W = group_sum<LPR>(W);
+        if (CE == 2) Z1 = group_sum<LPR>(Z1);
+
+        const RowCoef k = row_coefficients<DKD, CE>(A, ms, mt, Es, Et, W, zsg, ztg, m1, Z1);
+        if (live && sub == 0) {
+            acc_kd += (double)k.loss_kd;
+            if (CE != 0) acc_ce += (double)k.loss_ce;
+        }
+
+        // pass 3: gradient rows
+        float4 *pg = reinterpret_cast<float4 *>(A.gkd + r * A.ld_g);
+        float4 *pc = SPLIT ? reinterpret_cast<float4 *>(A.gce + r * A.ld_g) : nullptr;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int v = sub + i * LPR;
+            float4 gk, gc4;
+#define MDB200_P3(c)                                                   \
+    {                                                                  \
+        gk.c = fmaf(k.cs, s[i].c, -k.ct * t[i].c);                     \
+        if (CE != 0) {                                                 \
+            const float ce = k.cce * (CE == 2 ? c1[CE == 2 ? i : 0].c : s[i].c); \
+            if (SPLIT) gc4.c = ce; else gk.c += ce;                    \
+        }                                                              \
+    }
+            MDB200_P3(x) MDB200_P3(y) MDB200_P3(z) MDB200_P3(w)
+#undef MDB200_P3
+            if (v == gv) {
+                const float add_kd = k.gt_kd + ((CE != 0 && !SPLIT) ? k.gt_ce : 0.f);
+                if (gc == 0) { gk.x += add_kd; if (SPLIT) gc4.x += k.gt_ce; }
+                else if (gc == 1) { gk.y += add_kd; if (SPLIT) gc4.y += k.gt_ce; }
+                else if (gc == 2) { gk.z += add_kd; if (SPLIT) gc4.z += k.gt_ce; }
+                else { gk.w += add_kd; if (SPLIT) gc4.w += k.gt_ce; }
+            }
+            if (live && v < nvec) {
+                st_stream(pg + v, gk);
+                if (SPLIT) st_stream(pc + v, gc4);
+            }
+        }
+    }
+    cta_reduce_and_publish(A, acc_kd, acc_ce);
+}
+
+// ---------------------------------------------------------------------------------------
+// Generic kernel: any class count / alignment.  One CTA per row, three sweeps over the
+// row (the 2nd and 3rd hit L1/L2), scalar coalesced accesses.
+// ---------------------------------------------------------------------------------------
+template <typename Op>
+__device__ __forceinline__ float cta_allreduce(float v, float *sh, Op op, float ident) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = op(v, __shfl_xor_sync(0xffffffffu, v, o));
+    __syncthreads();  // protect sh from the previous use
+    if (lane == 0) sh[warp] = v;
+    __syncthreads();
+    float r = ident;
+    for (int w = 0; w < kLossWarps; ++w) r = op(r, sh[w]);
+    return r;
+}
+
+template <bool DKD, int CE, bool SPLIT>
+__global__ void __launch_bounds__(kLossThreads) loss_rows_generic(const LossArgs A) {
+    __shared__ float sh[kLossWarps];
+    const auto fmax_op = [](float a, float b) { return fmaxf(a, b); };
+    const auto add_op = [](float a, float b) { return a + b; };
+    constexpr float kLog2e = 1.4426950408889634f;
+    const int C = (int)A.classes;
+    double acc_kd = 0.0, acc_ce = 0.0;
+    for (long long r = blockIdx.x; r < A.rows; r += gridDim.x) {
+        const float *zs = A.zs + r * A.ld_s;
+        const float *zt = A.zt + r * A.ld_t;
+        const long long gl = A.target[r];
+        const int g = (gl >= 0 && gl < A.classes) ? (int)gl : -1;
+        const float zsg = g >= 0 ? __ldg(zs + g) : kNegBig;
+        const float ztg = g >= 0 ? __ldg(zt + g) : kNegBig;
+        float ms = kNegBig, mt = kNegBig;
+        for (int j = threadIdx.x; j < C; j += kLossThreads) {
+            if (DKD && j == g) continue;
+            ms = fmaxf(ms, __ldg(zs + j));
+            mt = fmaxf(mt, __ldg(zt + j));
+        }
+        ms = cta_allreduce(ms, sh, fmax_op, kNegBig);
+        mt = cta_allreduce(mt, sh, fmax_op, kNegBig);
+        const float m1 = fmaxf(ms, zsg);
+        float Es = 0.f, Et = 0.f, W = 0.f, Z1 = 0.f;
+        for (int j = threadIdx.x; j < C; j += kLossThreads) {
+            if (DKD && j == g) continue;
+            const float a = __ldg(zs + j), b = __ldg(zt + j);
+            const float ds = a - ms, dt = b - mt;
+            const float es = ex2_approx(ds * A.k2), et = ex2_approx(dt * A.k2);
+            Es += es;
+            Et += et;
+            W = fmaf(et, dt - ds, W);
+            if (CE == 2) Z1 += ex2_approx((a - m1) * kLog2e);
+        }
+        Es = cta_allreduce(Es, sh, add_op, 0.f);
+        Et = cta_allreduce(Et, sh, add_op, 0.f);
+        W = cta_allreduce(W, sh, add_op, 0.f);
+        if (CE == 2) Z1 = cta_allreduce(Z1, sh, add_op, 0.f);
+        const RowCoef k = row_coefficients<DKD, CE>(A, ms, mt, Es, Et, W, zsg, ztg, m1, Z1);
+        if (threadIdx.x == 0) {
+            acc_kd += (double)k.loss_kd;
+            if (CE != 0) acc_ce += (double)k.loss_ce;
+        }
+        float *gk = A.gkd + r * A.ld_g;
+        float *gc = SPLIT ? A.gce + r * A.ld_g : nullptr;
+        for (int j = threadIdx.x; j < C; j += kLossThreads) {
+            const bool at_label = (j == g);
+            float vk, vc = 0.f;
+            const float a = __ldg(zs + j), b = __ldg(zt + j);
+            if (DKD && at_label) {
+                vk = k.gt_kd;
+                if (CE != 0) vc = k.gt_ce;
+            } else {
+                const float es = ex2_approx((a - ms) * A.k2), et = ex2_approx((b - mt) * A.k2);
+                vk = fmaf(k.cs, es, -k.ct * et);
+                if (CE == 1) vc = k.cce * es;
+                if (CE == 2) vc = k.cce * ex2_approx((a - m1) * kLog2e);
+                if (at_label) {
+                    vk += k.gt_kd;
+                    vc += k.gt_ce;
+                }
+            }
+            if (CE != 0 && !SPLIT) vk += vc;
+            gk[j] = vk;
+            if (SPLIT) gc[j] = vc;
+        }
+    }
+    cta_reduce_and_publish(A, acc_kd, acc_ce);
+}
+
+__global__ void scale_by_scalar_kernel(float *out, const float *g, const float *up, long long n) {
+    const float s = __ldg(up);
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool vec = ((reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(g)) & 15u) == 0;
+    if (vec) {
+        const long long n4 = n >> 2;
+        for (long long i = i0; i < n4; i += stride) {
+            float4 v = reinterpret_cast<const float4 *>(g)[i];
+            v.x *= s; v.y *= s; v.z *= s; v.w *= s;
+            reinterpret_cast<float4 *>(out)[i] = v;
+        }
+        for (long long i = (n4 << 2) + i0; i < n; i += stride) out[i] = g[i] * s;
+    } else {
+        for (long long i = i0; i < n; i += stride) out[i] = g[i] * s;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// host-side dispatch
+// ---------------------------------------------------------------------------------------
+template <int LPR, int NV, bool DKD, int CE, bool SPLIT>
+static cudaError_t launch_regs(const LossArgs &A, int sms, cudaStream_t st) {
+    constexpr int rows_per_cta = kLossWarps * (32 / LPR);
+    long long want = (A.rows + rows_per_cta - 1) / rows_per_cta;
+    const long long cap = (long long)sms * (NV >= 16 ? 2 : (NV >= 8 ? 4 : 8));
+    if (want > cap) want = cap;
+    if (want > kMaxCtas) want = kMaxCtas;
+    loss_rows_in_registers<LPR, NV, DKD, CE, SPLIT><<<(unsigned)want, kLossThreads, 0, st>>>(A);
+    return cudaGetLastError();
+}
+
+template <bool DKD, int CE, bool SPLIT>
+static cudaError_t launch_shape(const LossArgs &A, bool vec_ok, int sms, cudaStream_t st) {
+    const long long nvec = A.classes >> 2;
+    if (vec_ok && nvec <= 32) return launch_regs<8, 4, DKD, CE, SPLIT>(A, sms, st);
+    if (vec_ok && nvec <= 128) return launch_regs<32, 4, DKD, CE, SPLIT>(A, sms, st);
+    if (vec_ok && nvec <= 256) return launch_regs<32, 8, DKD, CE, SPLIT>(A, sms, st);
+    if constexpr (CE != 2) {  // a third 64-float register row would spill: general-T CE goes generic there
+        if (vec_ok && nvec <= 512) return launch_regs<32, 16, DKD, CE, SPLIT>(A, sms, st);
+    }
+    long long want = A.rows;
+    const long long cap = (long long)sms * 8;
+    if (want > cap) want = cap;
+    if (want > kMaxCtas) want = kMaxCtas;
+    loss_rows_generic<DKD, CE, SPLIT><<<(unsigned)want, kLossThreads, 0, st>>>(A);
+    return cudaGetLastError();
+}
+
+template <bool DKD>
+static cudaError_t launch_ce(const LossArgs &A, int ce, bool split, bool vec_ok, int sms, cudaStream_t st) {
+    if (ce == 0) return launch_shape<DKD, 0, false>(A, vec_ok, sms, st);
+    if (ce == 1) return split ? launch_shape<DKD, 1, true>(A, vec_ok, sms, st)
+                              : launch_shape<DKD, 1, false>(A, vec_ok, sms, st);
+    return split ? launch_shape<DKD, 2, true>(A, vec_ok, sms, st)
+                 : launch_shape<DKD, 2, false>(A, vec_ok, sms, st);
+}
+
+}  // namespace mdb200
+
+using namespace mdb200;
+
+extern "C" size_t mdb200_loss_workspace_bytes(void) {
+    return kWorkspaceHeader + 2 * (size_t)kMaxCtas * sizeof(double);
+}
+
+extern "C" int mdb200_distill_loss(const float *z_student, const float *z_teacher, const int64_t *target,
+                                   int64_t rows, int64_t classes, int64_t ld_s, int64_t ld_t, int kind,
+                                   float alpha, float beta, float temperature, float kd_scale, int ce_mode,
+                                   float ce_scale, float *grad_kd, float *grad_ce, int64_t ld_g,
+                                   float *loss_out, void *workspace, size_t workspace_bytes, void *stream) {
+    if (!z_student || !z_teacher || !grad_kd || !loss_out) return MDB200_EINVAL;
+    if (rows <= 0 || classes <= 0 || !(temperature > 0.f)) return MDB200_EINVAL;
+    if (kind != MDB200_LOSS_DKD && kind != MDB200_LOSS_KD) return MDB200_EINVAL;
+    if (ce_mode < MDB200_CE_NONE || ce_mode > MDB200_CE_COMBINED) return MDB200_EINVAL;
+    if (ce_mode == MDB200_CE_SPLIT && !grad_ce) return MDB200_EINVAL;
+    if ((kind == MDB200_LOSS_DKD || ce_mode != MDB200_CE_NONE) && !target) return MDB200_EINVAL;
+    if (kind == MDB200_LOSS_DKD && classes < 2) return MDB200_EINVAL;
+    if (ld_s < classes || ld_t < classes || ld_g < classes) return MDB200_ESHAPE;
+    if (!workspace || workspace_bytes < mdb200_loss_workspace_bytes()) return MDB200_EWORKSPC;
+    if (!aligned4(z_student) || !aligned4(z_teacher) || !aligned4(grad_kd) || (grad_ce && !aligned4(grad_ce)) ||
+        !aligned16(workspace))
+        return MDB200_EALIGN;
+
+    LossArgs A;
+    A.zs = z_student;
+    A.zt = z_teacher;
+    A.target = reinterpret_cast<const long long *>(target);
+    A.gkd = grad_kd;
+    A.gce = grad_ce;
+    A.rows = rows;
+    A.classes = classes;
+    A.ld_s = ld_s;
+    A.ld_t = ld_t;
+    A.ld_g = ld_g;
+    A.alpha = alpha;
+    A.beta = beta;
+    A.inv_t = 1.0f / temperature;
+    A.k2 = (float)(1.4426950408889634 / (double)temperature);
+    A.c_kd = (float)((double)kd_scale * (double)temperature / (double)rows);
+    A.c_ce = (float)((double)ce_scale / (double)rows);
+    A.l_kd = (double)kd_scale * (double)temperature * (double)temperature / (double)rows;
+    A.l_ce = (ce_mode == MDB200_CE_NONE) ? 0.0 : (double)ce_scale / (double)rows;
+    A.ticket = reinterpret_cast<unsigned *>(workspace);
+    A.part = reinterpret_cast<double *>(reinterpret_cast<char *>(workspace) + kWorkspaceHeader);
+    A.loss_out = loss_out;
+
+    const bool split = ce_mode == MDB200_CE_SPLIT;
+    bool vec_ok = (classes % 4 == 0) && (ld_s % 4 == 0) && (ld_t % 4 == 0) && (ld_g % 4 == 0) &&
+                  aligned16(z_student) && aligned16(z_teacher) && aligned16(grad_kd) &&
+                  (!split || aligned16(grad_ce));
+    const int ce = ce_mode == MDB200_CE_NONE ? 0 : (temperature == 1.0f ? 1 : 2);
+    const int sms = sm_count();
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    cudaError_t e = (kind == MDB200_LOSS_DKD) ? launch_ce<true>(A, ce, split, vec_ok, sms, st)
+                                              : launch_ce<false>(A, ce, split, vec_ok, sms, st);
+    return (int)e;
+}
+
+extern "C" int mdb200_scale_by_device_scalar(float *out, const float *grad, const float *upstream, int64_t n,
+                                             void *stream) {
+    if (!out || !grad || !upstream || n < 0) return MDB200_EINVAL;
+    if (n == 0) return 0;
+    if (!aligned4(out) || !aligned4(grad)) return MDB200_EALIGN;
+    long long blocks = (n / 4 + 255) / 256;
+    const long long cap = (long long)sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    scale_by_scalar_kernel<<<(unsigned)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(out, grad, upstream, n);
+    return (int)cudaGetLastError();
+}

@@ -1,0 +1,59 @@
+"""Graft the B200 tail into an importable copy of the reference, leaving its files unchanged.
+
+    import mdistiller_ddp_b200 as b200
+    b200.install()                       # before tools/train.py builds distiller / trainer
+    runpy.run_path("tools/train.py", run_name="__main__")
+
+What gets replaced (and only this):
+  mdistiller.distillers.distiller_dict["DKD"|"KD"]       -> fused-tail distillers
+  mdistiller.distillers.DKD.dkd_loss / KD.kd_loss          -> kernel-backed functions (same signatures)
+  mdistiller.engine.dot.DistillationOrientedTrainer        -> flat / sharded optimizer
+  mdistiller.engine.trainer_dict["dot"|"base"]             -> subclasses of the reference's BaseTrainer
+                                                             with init_optimizer / train_iter from here
+"""
+
+from __future__ import annotations
+
+import importlib
+import sys
+
+
+def install(replace_base: bool = True):
+    """Returns the dict of patched objects; raises ImportError if `mdistiller` is not importable."""
+    from . import distillers, losses, optim
+    from .trainer import TailStepMixin
+
+    ref_distillers = importlib.import_module("mdistiller.distillers")
+    ref_engine = importlib.import_module("mdistiller.engine")
+    ref_trainer = importlib.import_module("mdistiller.engine.trainer")
+    ref_dot = importlib.import_module("mdistiller.engine.dot")
+
+    ref_distillers.distiller_dict["DKD"] = distillers.DKD
+    ref_distillers.distiller_dict["KD"] = distillers.KD
+    # `mdistiller.distillers.DKD` is the class (the package __init__ shadows the module name),
+    # so reach the modules through sys.modules to patch the free functions.
+    sys.modules["mdistiller.distillers.DKD"].dkd_loss = losses.dkd_loss
+    sys.modules["mdistiller.distillers.KD"].kd_loss = losses.kd_loss
+    ref_dot.DistillationOrientedTrainer = optim.DistillationOrientedTrainer
+    ref_trainer.DistillationOrientedTrainer = optim.DistillationOrientedTrainer
+
+    base = ref_trainer.BaseTrainer
+
+    class _RefHosted(TailStepMixin, base):
+        def __init__(self, experiment_name, distiller, train_loader, val_loader, cfg):
+            self.grad_clip = cfg.SOLVER.GRAD_CLIP       # needed by init_optimizer's callers early (D1)
+            self.use_amp = cfg.EXPERIMENT.AMP
+            base.__init__(self, experiment_name, distiller, train_loader, val_loader, cfg)
+
+    class DOT(_RefHosted):
+        trainer_kind = "dot"
+
+    class Base(_RefHosted):
+        trainer_kind = "base"
+
+    ref_engine.trainer_dict["dot"] = DOT
+    patched = {"DKD": distillers.DKD, "KD": distillers.KD, "dot": DOT}
+    if replace_base:
+        ref_engine.trainer_dict["base"] = Base
+        patched["base"] = Base
+    return patched

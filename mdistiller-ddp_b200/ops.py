@@ -1,0 +1,149 @@
+"""Tensor-level wrappers over the C-ABI: pointers out of torch tensors, nothing else.
+
+torch is used here for device memory and the current stream only.  Every function
+insists on CUDA fp32 tensors and raises otherwise -- there is no CPU path.
+"""
+
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import (CE_COMBINED, CE_NONE, CE_SPLIT, DOT_BOTH, DOT_KD_ONLY, DOT_TASK_ONLY,  # noqa: F401
+                   LOSS_DKD, LOSS_KD)
+
+_workspaces = {}
+launch_count = 0   # kernels of ours launched by this process (bench.py reports it)
+
+
+def _stream_ptr(device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def _need_cuda_f32(t: torch.Tensor, name: str) -> None:
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor: the distillation tail has no CPU fallback")
+    if t.dtype != torch.float32:
+        raise TypeError(f"{name} must be float32, got {t.dtype}")
+
+
+def loss_workspace(device: torch.device) -> torch.Tensor:
+    """Per (device, stream) reduction workspace, zeroed once (the kernel re-zeroes its ticket)."""
+    key = (device.index if device.index is not None else torch.cuda.current_device(),
+           torch.cuda.current_stream(device).cuda_stream)
+    ws = _workspaces.get(key)
+    if ws is None:
+        nbytes = _lib.load().mdb200_loss_workspace_bytes()
+        ws = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+def distill_loss(z_student: torch.Tensor, z_teacher: torch.Tensor, target: Optional[torch.Tensor], *,
+                 kind: int, alpha: float = 1.0, beta: float = 1.0, temperature: float = 1.0,
+                 kd_scale: float = 1.0, ce_mode: int = CE_NONE, ce_scale: float = 1.0,
+                 grad_kd: Optional[torch.Tensor] = None, grad_ce: Optional[torch.Tensor] = None,
+                 loss_out: Optional[torch.Tensor] = None
+                 ) -> Tuple[torch.Tensor, torch.Tensor, Optional[torch.Tensor]]:
+    """One launch: returns (loss_pair[2] = {kd, ce}, grad_kd, grad_ce or None)."""
+    global launch_count
+    lib = _lib.load()
+    _need_cuda_f32(z_student, "logits_student")
+    _need_cuda_f32(z_teacher, "logits_teacher")
+    if z_student.dim() != 2 or z_student.shape != z_teacher.shape:
+        raise ValueError(f"logits must be matching [rows, classes]; got {tuple(z_student.shape)} "
+                         f"and {tuple(z_teacher.shape)}")
+    if z_student.stride(1) != 1:
+        z_student = z_student.contiguous()
+    if z_teacher.stride(1) != 1:
+        z_teacher = z_teacher.contiguous()
+    rows, classes = z_student.shape
+    tptr = None
+    if target is not None:
+        if not target.is_cuda or target.dtype != torch.int64:
+            raise TypeError("target must be a CUDA int64 tensor")
+        target = target.reshape(-1).contiguous()
+        if target.numel() != rows:
+            raise ValueError("target length != rows")
+        tptr = target.data_ptr()
+    dev = z_student.device
+    if grad_kd is None:
+        grad_kd = torch.empty((rows, classes), dtype=torch.float32, device=dev)
+    if ce_mode == CE_SPLIT and grad_ce is None:
+        grad_ce = torch.empty((rows, classes), dtype=torch.float32, device=dev)
+    if loss_out is None:
+        loss_out = torch.empty(2, dtype=torch.float32, device=dev)
+    ws = loss_workspace(dev)
+    with torch.cuda.device(dev):
+        rc = lib.mdb200_distill_loss(
+            z_student.data_ptr(), z_teacher.data_ptr(), tptr, rows, classes,
+            z_student.stride(0), z_teacher.stride(0), kind, alpha, beta, temperature,
+            kd_scale, ce_mode, ce_scale, grad_kd.data_ptr(),
+            grad_ce.data_ptr() if (grad_ce is not None and ce_mode == CE_SPLIT) else None,
+            grad_kd.stride(0), loss_out.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr(dev))
+    _lib.check(rc, "mdb200_distill_loss")
+    launch_count += 1
+    return loss_out, grad_kd, (grad_ce if ce_mode == CE_SPLIT else None)
+
+
+def scale_by_device_scalar(grad: torch.Tensor, upstream: torch.Tensor,
+                           out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """out = grad * upstream (0-dim device tensor); no host sync."""
+    global launch_count
+    lib = _lib.load()
+    _need_cuda_f32(grad, "grad")
+    _need_cuda_f32(upstream, "upstream")
+    if not grad.is_contiguous():
+        grad = grad.contiguous()
+    if out is None:
+        out = torch.empty_like(grad)
+    with torch.cuda.device(grad.device):
+        rc = lib.mdb200_scale_by_device_scalar(out.data_ptr(), grad.data_ptr(), upstream.data_ptr(),
+                                               grad.numel(), _stream_ptr(grad.device))
+    _lib.check(rc, "mdb200_scale_by_device_scalar")
+    launch_count += 1
+    return out
+
+
+def _flat_ptr(t: Optional[torch.Tensor], name: str, n: int) -> Optional[int]:
+    if t is None:
+        return None
+    _need_cuda_f32(t, name)
+    if not t.is_contiguous() or t.numel() < n:
+        raise ValueError(f"{name} must be contiguous with at least {n} elements")
+    return t.data_ptr()
+
+
+def dot_step(p: torch.Tensor, g_task: Optional[torch.Tensor], g_kd: Optional[torch.Tensor],
+             v_task: Optional[torch.Tensor], v_kd: Optional[torch.Tensor], *, lr: float, momentum: float,
+             momentum_kd: float, weight_decay: float = 0.0, dampening: float = 0.0, grad_scale: float = 1.0,
+             first_task: bool = False, first_kd: bool = False, membership: int = DOT_BOTH,
+             n: Optional[int] = None) -> None:
+    """In-place DOT update of the flat range p[:n]."""
+    global launch_count
+    lib = _lib.load()
+    n = p.numel() if n is None else n
+    ptrs = (_flat_ptr(p, "p", n), _flat_ptr(g_task, "g_task", n), _flat_ptr(g_kd, "g_kd", n),
+            _flat_ptr(v_task, "v_task", n), _flat_ptr(v_kd, "v_kd", n))
+    with torch.cuda.device(p.device):
+        rc = lib.mdb200_dot_step(*ptrs, n, lr, momentum, momentum_kd, weight_decay, dampening, grad_scale,
+                                 int(first_task), int(first_kd), membership, _stream_ptr(p.device))
+    _lib.check(rc, "mdb200_dot_step")
+    launch_count += 1
+
+
+def sgd_step(p: torch.Tensor, g: torch.Tensor, v: Optional[torch.Tensor], *, lr: float, momentum: float,
+             weight_decay: float = 0.0, dampening: float = 0.0, grad_scale: float = 1.0,
+             first_step: bool = False, n: Optional[int] = None) -> None:
+    """In-place momentum-SGD update of the flat range p[:n]."""
+    global launch_count
+    lib = _lib.load()
+    n = p.numel() if n is None else n
+    ptrs = (_flat_ptr(p, "p", n), _flat_ptr(g, "g", n), _flat_ptr(v, "v", n))
+    with torch.cuda.device(p.device):
+        rc = lib.mdb200_sgd_step(*ptrs, n, lr, momentum, weight_decay, dampening, grad_scale, int(first_step),
+                                 _stream_ptr(p.device))
+    _lib.check(rc, "mdb200_sgd_step")
+    launch_count += 1

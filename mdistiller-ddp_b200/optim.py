@@ -1,0 +1,329 @@
+"""Flat-buffer optimizers: DOT's dual-momentum SGD and plain momentum SGD.
+
+``DistillationOrientedTrainer`` keeps the reference's constructor, ``step_kd()`` /
+``step()`` / ``zero_grad()`` protocol, ``param_groups[0]["lr"]`` mutability and
+``state_dict()`` layout (mdistiller/engine/dot.py:58-174), but stores parameters,
+the two gradient sets and the two momentum buffers as flat fp32 buffers so one
+sm_100a launch updates everything (434 launches per step for ResNet18 in the
+reference).  With ``torch.distributed`` initialised it is also the data-parallel
+step: reduce-scatter(KD bucket) -> reduce-scatter(task bucket) -> update on the rank's
+shard -> all-gather(parameters), replacing DDP's all-reduce + the optimizer loop
+(tools/train.py:86, trainer.py:427-432).
+
+How the two gradient sets get into flat buckets without extra copies: ``zero_grad``
+zeroes the bucket of the coming backward and points every ``p.grad`` at its slice, so
+autograd accumulates straight into the bucket.  A parameter counts as "has a gradient"
+for a pass (dot.py:112,144 test ``p.grad is not None``) if autograd touched it in that
+pass (post-accumulate hook) or the caller assigned a gradient tensor of its own, which
+is then copied into the bucket.
+"""
+
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+from torch.optim.optimizer import Optimizer, required
+
+from . import ops
+from .comm import ShardComm
+from .flat import FlatSpace
+
+_NONE, _TASK, _KD, _BOTH = 0, 1, 2, 3
+_MEMBERSHIP = {_BOTH: ops.DOT_BOTH, _TASK: ops.DOT_TASK_ONLY, _KD: ops.DOT_KD_ONLY}
+
+
+class _FlatOptimizer(Optimizer):
+    """Shared plumbing: flat space, gradient buckets, membership tracking, sharding."""
+
+    _bucket_names: Tuple[str, ...] = ()
+
+    def __init__(self, params, defaults, comm: Optional[ShardComm], kernels):
+        super().__init__(params, defaults)
+        assert len(self.param_groups) == 1, "Only implement for one-group params."
+        self._k = kernels if kernels is not None else ops
+        self._comm = comm if comm is not None else ShardComm()
+        plist = self.param_groups[0]["params"]
+        self._space = FlatSpace(plist, self._comm.world_size, self._comm.rank)
+        self._comm.broadcast(self._space.flat, src=0)       # DDP's constructor does the same
+        self._buckets: Dict[str, torch.Tensor] = {}
+        self._views: Dict[str, List[torch.Tensor]] = {}
+        for name in self._bucket_names:
+            b = self._space.new_buffer()
+            self._buckets[name] = b
+            self._views[name] = self._space.views(b)
+        self._phase = self._bucket_names[0]
+        self._touched = set()
+        self._index = {id(p): i for i, p in enumerate(plist)}
+        self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in plist if p.requires_grad]
+        self._run_cache: Dict[tuple, list] = {}
+
+    # -- gradient capture ----------------------------------------------------------
+    def _on_grad(self, p: torch.Tensor) -> None:
+        self._touched.add(self._index[id(p)])
+
+    def _arm(self, name: str) -> None:
+        """Zero bucket `name` and make it the accumulation target of the next backward."""
+        self._buckets[name].zero_()
+        for p, v in zip(self._space.params, self._views[name]):
+            p.grad = v
+        self._touched.clear()
+
+    def zero_grad(self, set_to_none: bool = True) -> None:  # noqa: D401 - same signature as torch's
+        # `set_to_none` is accepted for drop-in compatibility: the reference protocol only needs
+        # "no stale gradient survives", which a zeroed bucket guarantees.
+        self._arm(self._phase)
+
+    def _collect(self, name: str) -> List[bool]:
+        """Which parameters have a gradient for this pass; foreign tensors are copied in."""
+        views = self._views[name]
+        has = []
+        for i, (p, v) in enumerate(zip(self._space.params, views)):
+            g = p.grad
+            if g is None:
+                has.append(False)
+            elif g.data_ptr() == v.data_ptr() and g.shape == v.shape:
+                has.append(i in self._touched)
+            else:
+                v.copy_(g)
+                has.append(True)
+        return has
+
+    # -- runs of tensors sharing one update rule --------------------------------------
+    def _runs(self, modes: Sequence[tuple]) -> list:
+        """Merge consecutive tensors with equal `modes[i]` into (lo, hi, mode) element ranges,
+        clipped to this rank's shard."""
+        key = tuple(modes)
+        cached = self._run_cache.get(key)
+        if cached is not None:
+            return cached
+        sp = self._space
+        runs = []
+        i, n = 0, len(modes)
+        while i < n:
+            j = i
+            while j + 1 < n and modes[j + 1] == modes[i]:
+                j += 1
+            lo, hi = sp.clip_to_shard(sp.offsets[i], sp.ends[j])
+            if hi > lo and modes[i][0] != _NONE:
+                runs.append((lo, hi, modes[i]))
+            i = j + 1
+        if len(self._run_cache) > 64:
+            self._run_cache.clear()
+        self._run_cache[key] = runs
+        return runs
+
+    @property
+    def flat_params(self) -> torch.Tensor:
+        return self._space.flat
+
+    @property
+    def world_size(self) -> int:
+        return self._comm.world_size
+
+    # -- checkpoint format -------------------------------------------------------------
+    def _full_momentum(self, shard_buf: torch.Tensor) -> torch.Tensor:
+        """Gather a sharded momentum buffer into a full-length flat tensor."""
+        full = self._space.new_buffer()
+        self._space.shard(full).copy_(shard_buf)
+        self._comm.all_gather(full)
+        return full
+
+    def _export_state(self, pairs: Sequence[Tuple[str, torch.Tensor, List[bool]]]) -> None:
+        self.state.clear()
+        for key, shard_buf, has in pairs:
+            if not any(has):
+                continue
+            full = self._full_momentum(shard_buf)
+            for p, v, h in zip(self._space.params, self._space.views(full), has):
+                if h:
+                    self.state[p][key] = v.clone()
+
+    def _import_state(self, pairs: Sequence[Tuple[str, torch.Tensor, List[bool]]]) -> None:
+        sp = self._space
+        for key, shard_buf, has in pairs:
+            full = sp.new_buffer()
+            for i, (p, v) in enumerate(zip(sp.params, sp.views(full))):
+                t = self.state.get(p, {}).get(key)
+                has[i] = t is not None
+                if t is not None:
+                    v.copy_(t.to(v.dtype))
+            shard_buf.copy_(sp.shard(full))
+        self.state.clear()
+
+
+class DistillationOrientedTrainer(_FlatOptimizer):
+    r"""Distillation-Oriented Trainer (drop-in for mdistiller/engine/dot.py:58-174).
+
+    Usage is the reference's::
+
+        optimizer.zero_grad(set_to_none=True)
+        loss_kd.backward(retain_graph=True)
+        optimizer.step_kd()      # KD gradients captured (and, multi-GPU, reduce-scattered)
+        optimizer.zero_grad(set_to_none=True)
+        loss_task.backward()
+        optimizer.step()         # both momenta and the parameters updated in one launch
+    """
+
+    _bucket_names = ("kd", "task")
+
+    def __init__(self, params, lr=required, momentum=0, momentum_kd=0, dampening=0, weight_decay=0, *,
+                 comm: Optional[ShardComm] = None, kernels=None):
+        if lr is not required and lr < 0.0:
+            raise ValueError("Invalid learning rate: {}".format(lr))
+        if momentum < 0.0:
+            raise ValueError("Invalid momentum value: {}".format(momentum))
+        if momentum_kd < 0.0:
+            raise ValueError("Invalid momentum kd value: {}".format(momentum_kd))
+        if weight_decay < 0.0:
+            raise ValueError("Invalid weight_decay value: {}".format(weight_decay))
+        defaults = dict(lr=lr, momentum=momentum, momentum_kd=momentum_kd, dampening=dampening,
+                        weight_decay=weight_decay)
+        super().__init__(params, defaults, comm, kernels)
+        n = len(self._space.params)
+        self._v_task = self._space.new_shard_buffer()
+        self._v_kd = self._space.new_shard_buffer()
+        self._has_vt = [False] * n     # 'momentum_buffer' exists (dot.py:165-167)
+        self._has_vk = [False] * n     # 'momentum_kd_buffer' exists (dot.py:168-170)
+        self._kd_members: Optional[List[bool]] = None
+        self._kd_work = None
+
+    @torch.no_grad()
+    def step_kd(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        assert len(self.param_groups) == 1, "Only implement for one-group params."
+        self._kd_members = self._collect("kd")
+        # the KD bucket is complete: start its reduce-scatter now so it overlaps backward #2
+        self._kd_work = self._comm.reduce_scatter_sum(self._buckets["kd"], async_op=True)
+        self._phase = "task"
+        return loss
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        assert len(self.param_groups) == 1, "Only implement for one-group params."
+        group = self.param_groups[0]
+        task_members = self._collect("task")
+        kd_members = self._kd_members if self._kd_members is not None else [False] * len(task_members)
+        work = self._comm.reduce_scatter_sum(self._buckets["task"], async_op=True)
+        for w in (self._kd_work, work):
+            if w is not None:
+                w.wait()
+        self._kd_work = None
+
+        modes = []
+        for i, (t, k) in enumerate(zip(task_members, kd_members)):
+            m = (_BOTH if k else _TASK) if t else (_KD if k else _NONE)
+            modes.append((m, t and not self._has_vt[i], k and not self._has_vk[i]))
+        sp = self._space
+        momentum = group["momentum"]
+        for lo, hi, (m, first_t, first_k) in self._runs(modes):
+            a, b = lo - sp.shard_lo, hi - sp.shard_lo
+            self._k.dot_step(
+                sp.flat[lo:hi],
+                self._buckets["task"][lo:hi] if m != _KD else None,
+                self._buckets["kd"][lo:hi] if m != _TASK else None,
+                self._v_task[a:b] if (m != _KD and momentum != 0) else None,
+                self._v_kd[a:b] if m != _TASK else None,
+                lr=group["lr"], momentum=momentum, momentum_kd=group["momentum_kd"],
+                weight_decay=group["weight_decay"], dampening=group["dampening"],
+                grad_scale=1.0 / self._comm.world_size, first_task=first_t, first_kd=first_k,
+                membership=_MEMBERSHIP[m])
+        self._comm.all_gather(sp.flat)
+
+        for i, (t, k) in enumerate(zip(task_members, kd_members)):
+            if t and momentum != 0:
+                self._has_vt[i] = True
+            if k:
+                self._has_vk[i] = True
+        self._kd_members = None
+        self._phase = "kd"
+        return loss
+
+    # -- reference checkpoint layout: state[p]['momentum_buffer'|'momentum_kd_buffer'] -----
+    def state_dict(self):
+        self._export_state((("momentum_buffer", self._v_task, self._has_vt),
+                            ("momentum_kd_buffer", self._v_kd, self._has_vk)))
+        try:
+            return super().state_dict()
+        finally:
+            self.state.clear()
+
+    def load_state_dict(self, state_dict):
+        super().load_state_dict(state_dict)
+        self._import_state((("momentum_buffer", self._v_task, self._has_vt),
+                            ("momentum_kd_buffer", self._v_kd, self._has_vk)))
+        self._run_cache.clear()
+
+    def momentum_views(self):
+        """Per-parameter views of the (unsharded) momentum buffers -- single-process use."""
+        if self._comm.world_size != 1:
+            raise RuntimeError("momentum is sharded; use state_dict()")
+        return self._space.views(self._v_task), self._space.views(self._v_kd)
+
+
+class FlatSGD(_FlatOptimizer):
+    """torch.optim.SGD(momentum, weight_decay, dampening; no Nesterov) on the flat space --
+    the optimizer BaseTrainer.init_optimizer builds for SOLVER.TYPE == 'SGD'
+    (mdistiller/engine/trainer.py:86-91), plus the sharded gradient sync."""
+
+    _bucket_names = ("grad",)
+
+    def __init__(self, params, lr=required, momentum=0, dampening=0, weight_decay=0, *,
+                 comm: Optional[ShardComm] = None, kernels=None):
+        if lr is not required and lr < 0.0:
+            raise ValueError("Invalid learning rate: {}".format(lr))
+        if momentum < 0.0:
+            raise ValueError("Invalid momentum value: {}".format(momentum))
+        if weight_decay < 0.0:
+            raise ValueError("Invalid weight_decay value: {}".format(weight_decay))
+        defaults = dict(lr=lr, momentum=momentum, dampening=dampening, weight_decay=weight_decay)
+        super().__init__(params, defaults, comm, kernels)
+        self._v = self._space.new_shard_buffer()
+        self._has_v = [False] * len(self._space.params)
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        group = self.param_groups[0]
+        members = self._collect("grad")
+        work = self._comm.reduce_scatter_sum(self._buckets["grad"], async_op=True)
+        if work is not None:
+            work.wait()
+        momentum = group["momentum"]
+        modes = [((_TASK if t else _NONE), t and not self._has_v[i], False) for i, t in enumerate(members)]
+        sp = self._space
+        for lo, hi, (_, first, _) in self._runs(modes):
+            a, b = lo - sp.shard_lo, hi - sp.shard_lo
+            self._k.sgd_step(sp.flat[lo:hi], self._buckets["grad"][lo:hi],
+                             self._v[a:b] if momentum != 0 else None,
+                             lr=group["lr"], momentum=momentum, weight_decay=group["weight_decay"],
+                             dampening=group["dampening"], grad_scale=1.0 / self._comm.world_size,
+                             first_step=first)
+        self._comm.all_gather(sp.flat)
+        if momentum != 0:
+            for i, t in enumerate(members):
+                if t:
+                    self._has_v[i] = True
+        return loss
+
+    def state_dict(self):
+        self._export_state((("momentum_buffer", self._v, self._has_v),))
+        try:
+            return super().state_dict()
+        finally:
+            self.state.clear()
+
+    def load_state_dict(self, state_dict):
+        super().load_state_dict(state_dict)
+        self._import_state((("momentum_buffer", self._v, self._has_v),))
+        self._run_cache.clear()

@@ -1,0 +1,167 @@
+"""Per-iteration training step for the DOT and base trainers, B200 path.
+
+Mirrors the hot section of the reference engine and nothing else:
+  DOT.init_optimizer / DOT.train_iter      mdistiller/engine/trainer.py:376-391, 412-461
+  BaseTrainer.init_optimizer / train_iter  mdistiller/engine/trainer.py:83-110, 257-321
+Epoch loop, logging, validation and checkpoints stay the reference's (out of scope);
+``install.py`` grafts these methods onto the reference's ``BaseTrainer`` so an unchanged
+``tools/train.py`` picks them up through ``trainer_dict``.
+
+Differences from the reference, all documented reference defects:
+  D1/D2  m_task = SGD.MOMENTUM - DOT.DELTA, m_kd = SGD.MOMENTUM + DOT.DELTA, AMP read from cfg.
+  D3     both gradient sets are averaged across ranks (the reference syncs only the KD one).
+  D4     only student parameters are communicated (DDP's reducer is switched off).
+"""
+
+from __future__ import annotations
+
+import time
+from typing import Dict, Optional
+
+import torch
+import torch.distributed as dist
+
+from .comm import ShardComm
+from .optim import DistillationOrientedTrainer, FlatSGD
+
+
+def _unwrap(distiller):
+    return distiller.module if hasattr(distiller, "module") else distiller
+
+
+def silence_ddp_reducer(distiller) -> None:
+    """An already DDP-wrapped distiller (tools/train.py:86) must not all-reduce on its own:
+    the flat buckets are reduce-scattered by the optimizer instead."""
+    if hasattr(distiller, "require_backward_grad_sync"):
+        distiller.require_backward_grad_sync = False
+
+
+class _Meter:
+    def __init__(self):
+        self.val = self.avg = self.sum = self.count = 0
+
+    def update(self, val, n=1):
+        self.val = val
+        self.sum += val * n
+        self.count += n
+        self.avg = self.sum / self.count
+
+
+def new_train_meters() -> Dict:
+    return {"training_time": _Meter(), "data_time": _Meter(), "losses": dict(), "top1": _Meter(), "top5": _Meter()}
+
+
+class TailStepMixin:
+    """`init_optimizer` + `train_iter` for both trainers; host class supplies
+    ``self.distiller``, ``self.cfg`` and (after init) ``self.optimizer``."""
+
+    trainer_kind = "dot"   # "dot" | "base"
+
+    # ---------------------------------------------------------------- optimizer
+    def init_optimizer(self, cfg):
+        core = _unwrap(self.distiller)
+        silence_ddp_reducer(self.distiller)
+        comm = ShardComm() if (dist.is_available() and dist.is_initialized()) else None
+        params = core.get_learnable_parameters()
+        if self.trainer_kind == "dot":
+            if cfg.EXPERIMENT.AMP:
+                raise NotImplementedError("AMP is not supported for DOT.")
+            if cfg.SOLVER.TYPE != "SGD":
+                raise NotImplementedError(cfg.SOLVER.TYPE)
+            return DistillationOrientedTrainer(
+                params, lr=cfg.SOLVER.LR,
+                momentum=cfg.SOLVER.SGD.MOMENTUM - cfg.SOLVER.DOT.DELTA,
+                momentum_kd=cfg.SOLVER.SGD.MOMENTUM + cfg.SOLVER.DOT.DELTA,
+                weight_decay=cfg.SOLVER.WEIGHT_DECAY, comm=comm)
+        if cfg.SOLVER.TYPE != "SGD":
+            raise NotImplementedError(f"{cfg.SOLVER.TYPE}: only the SGD solver has a flat sm_100a step")
+        if cfg.EXPERIMENT.AMP:
+            raise NotImplementedError("AMP is outside the fp32 distillation tail")
+        core.combined_tail = True     # one gradient buffer: the base trainer sums the losses anyway
+        return FlatSGD(params, lr=cfg.SOLVER.LR, momentum=cfg.SOLVER.SGD.MOMENTUM,
+                       weight_decay=cfg.SOLVER.WEIGHT_DECAY, comm=comm)
+
+    # ---------------------------------------------------------------- one iteration
+    def train_iter(self, data, epoch, train_meters):
+        t0 = time.time()
+        image, target, index = data
+        train_meters["data_time"].update(time.time() - t0)
+        image = image.float().cuda(non_blocking=True)
+        target = target.cuda(non_blocking=True)
+        preds, losses = self.tail_step(image, target, epoch)
+        train_meters["training_time"].update(time.time() - t0)
+        return self.report(preds, target, losses, epoch, train_meters)
+
+    def tail_step(self, image, target, epoch):
+        """forward -> backward(s) -> optimizer; returns (logits, {'loss_ce','loss_kd'}) on device."""
+        opt = self.optimizer
+        core = _unwrap(self.distiller)
+        if self.trainer_kind == "dot":
+            preds, losses = self.distiller(image=image, target=target, epoch=epoch)
+            tail = getattr(core, "last_tail", None)
+            opt.zero_grad(set_to_none=True)
+            if tail is not None and not tail.combined:
+                # seed both backwards with the gradients the fused launch already produced
+                torch.autograd.backward([tail.logits], [tail.grad_kd], retain_graph=True)
+                opt.step_kd()
+                opt.zero_grad(set_to_none=True)
+                torch.autograd.backward([tail.logits], [tail.grad_ce])
+            else:
+                losses["loss_kd"].backward(retain_graph=True)
+                opt.step_kd()
+                opt.zero_grad(set_to_none=True)
+                losses["loss_ce"].backward()
+            opt.step()
+        else:
+            opt.zero_grad()
+            preds, losses = self.distiller(image=image, target=target, epoch=epoch)
+            tail = getattr(core, "last_tail", None)
+            if tail is not None and tail.combined:
+                torch.autograd.backward([tail.logits], [tail.grad_kd])
+            else:
+                sum(losses.values()).backward()
+            if getattr(self, "grad_clip", 0.0) and self.grad_clip > 0:
+                raise NotImplementedError("SOLVER.GRAD_CLIP is not part of the flat step yet")
+            opt.step()
+        if tail is not None:
+            core.last_tail = None
+        return preds, losses
+
+    # ---------------------------------------------------------------- metrics (one collective, one D2H)
+    @torch.no_grad()
+    def report(self, preds, target, losses, epoch, train_meters):
+        """Cross-rank loss means and top-1/top-5 for the progress line (trainer.py:436-461):
+        local counts are packed into one tensor, summed with ONE all-reduce and read back with
+        ONE device-to-host copy (the reference does 2 all-gathers + 4 all-reduces + 4 syncs)."""
+        batch = target.shape[0]
+        k = min(5, preds.shape[1])
+        top = preds.topk(k, dim=1).indices
+        hit = top.eq(target.view(-1, 1))
+        pack = torch.stack([losses["loss_ce"].detach().float(), losses["loss_kd"].detach().float(),
+                            hit[:, 0].sum().float(), hit.sum().float(),
+                            torch.tensor(float(batch), device=preds.device)])
+        world = 1
+        if dist.is_available() and dist.is_initialized():
+            dist.all_reduce(pack)
+            world = dist.get_world_size()
+        ce, kd, c1, c5, n = pack.cpu().tolist()
+        vals = {"loss_ce": ce / world, "loss_kd": kd / world, "_total": (ce + kd) / world}
+        n = int(n)
+        for name, v in vals.items():
+            train_meters["losses"].setdefault(name, _Meter()).update(v, n)
+        train_meters["top1"].update(100.0 * c1 / n, n)
+        train_meters["top5"].update(100.0 * c5 / n, n)
+        return "Epoch:{}| Time(data):{:.3f}| Time(train):{:.3f}| Loss:{:.4f}| Top-1:{:.3f}| Top-5:{:.3f}".format(
+            epoch, train_meters["data_time"].avg, train_meters["training_time"].avg,
+            train_meters["losses"]["_total"].avg, train_meters["top1"].avg, train_meters["top5"].avg)
+
+
+class StandaloneTrainer(TailStepMixin):
+    """Minimal host for the mixin when the reference engine is not around (bench, smoke, tests)."""
+
+    def __init__(self, distiller, cfg, kind: Optional[str] = None):
+        self.distiller = distiller
+        self.cfg = cfg
+        self.trainer_kind = kind or cfg.SOLVER.TRAINER
+        self.grad_clip = getattr(cfg.SOLVER, "GRAD_CLIP", 0.0)
+        self.optimizer = self.init_optimizer(cfg)

@@ -1,0 +1,149 @@
+"""Synthetic workloads for smoke / bench / tests: backbones with the reference's call
+contract and random data of the benchmark shapes.
+
+The distillation tail treats backbones as opaque ``nn.Module``s returning
+``(logits, feature_dict)``; in a real run they are the reference's own modules
+(out of scope here).  The GPU box has no copy of the reference, so
+the benchmark instantiates architecture-equivalent stand-ins: torchvision's ResNet-18/
+34/50 for the ImageNet configs (same parameter counts as the reference's
+models/imagenet/resnet.py: 11 689 512 / 21 797 672 / 25 557 032) and a small
+CIFAR-style residual net for the ``resnet8x4`` / ``resnet32x4`` configs
+(1 233 540 / 7 433 860 parameters, as the reference's).  Weights are random-init.
+"""
+
+from __future__ import annotations
+
+from types import SimpleNamespace
+from typing import Tuple
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+class _WithFeats(nn.Module):
+    """Adapt a plain classifier to the ``(logits, feats)`` return convention."""
+
+    def __init__(self, net: nn.Module):
+        super().__init__()
+        self.net = net
+
+    def forward(self, x):
+        return self.net(x), {}
+
+
+def imagenet_resnet(name: str, num_classes: int = 1000) -> nn.Module:
+    import torchvision.models as tvm
+
+    ctor = {"ResNet18": tvm.resnet18, "ResNet34": tvm.resnet34, "ResNet50": tvm.resnet50}[name]
+    return _WithFeats(ctor(weights=None, num_classes=num_classes))
+
+
+class _Unit(nn.Module):
+    """Two 3x3 conv-bn pairs with an identity or 1x1-projected skip."""
+
+    def __init__(self, cin: int, cout: int, stride: int):
+        super().__init__()
+        self.c1 = nn.Conv2d(cin, cout, 3, stride, 1, bias=False)
+        self.n1 = nn.BatchNorm2d(cout)
+        self.c2 = nn.Conv2d(cout, cout, 3, 1, 1, bias=False)
+        self.n2 = nn.BatchNorm2d(cout)
+        self.skip = None
+        if stride != 1 or cin != cout:
+            self.skip = nn.Sequential(nn.Conv2d(cin, cout, 1, stride, bias=False), nn.BatchNorm2d(cout))
+
+    def forward(self, x):
+        y = F.relu(self.n1(self.c1(x)))
+        y = self.n2(self.c2(y))
+        return F.relu(y + (x if self.skip is None else self.skip(x)))
+
+
+class CifarResNet(nn.Module):
+    """depth = 6n+2 CIFAR residual net; widths (w0, w1, w2, w3) = stem and three stages."""
+
+    def __init__(self, depth: int, widths: Tuple[int, int, int, int], num_classes: int = 100):
+        super().__init__()
+        assert (depth - 2) % 6 == 0
+        n = (depth - 2) // 6
+        self.stem = nn.Sequential(nn.Conv2d(3, widths[0], 3, 1, 1, bias=False), nn.BatchNorm2d(widths[0]))
+        units, cin = [], widths[0]
+        for stage, cout in enumerate(widths[1:]):
+            for u in range(n):
+                units.append(_Unit(cin, cout, 2 if (u == 0 and stage > 0) else 1))
+                cin = cout
+        self.units = nn.Sequential(*units)
+        self.head = nn.Linear(cin, num_classes)
+
+    def forward(self, x):
+        x = self.units(F.relu(self.stem(x)))
+        pooled = torch.flatten(F.adaptive_avg_pool2d(x, 1), 1)
+        return self.head(pooled), {"pooled_feat": pooled}
+
+
+def cifar_resnet(name: str, num_classes: int = 100) -> nn.Module:
+    depth = {"resnet8x4": 8, "resnet32x4": 32}[name]
+    return CifarResNet(depth, (32, 64, 128, 256), num_classes)
+
+
+class TinyNet(nn.Module):
+    """A few thousand parameters; for smoke() and unit tests."""
+
+    def __init__(self, num_classes: int = 100, width: int = 16):
+        super().__init__()
+        self.conv = nn.Conv2d(3, width, 3, 2, 1, bias=False)
+        self.norm = nn.BatchNorm2d(width)
+        self.head = nn.Linear(width, num_classes)
+
+    def forward(self, x):
+        f = torch.flatten(F.adaptive_avg_pool2d(F.relu(self.norm(self.conv(x))), 1), 1)
+        return self.head(f), {"pooled_feat": f}
+
+
+WORKLOADS = {
+    # name: (teacher, student, builder, image hw, classes, distiller, trainer, per-GPU batch)
+    "imagenet_r34_r18_dkd_dot": ("ResNet34", "ResNet18", imagenet_resnet, 224, 1000, "DKD", "dot", 256),
+    "imagenet_r34_r18_kd_dot": ("ResNet34", "ResNet18", imagenet_resnet, 224, 1000, "KD", "dot", 256),
+    "cifar_res32x4_res8x4_kd_dot": ("resnet32x4", "resnet8x4", cifar_resnet, 32, 100, "KD", "dot", 64),
+    "cifar_res32x4_res8x4_dkd_base": ("resnet32x4", "resnet8x4", cifar_resnet, 32, 100, "DKD", "base", 64),
+}
+
+
+def default_cfg(workload: str = "imagenet_r34_r18_dkd_dot") -> SimpleNamespace:
+    """The hyper-parameters of the reference yaml each workload stands for
+    (configs/imagenet/r34_r18/{dkd,dot}.yaml, configs/cifar100/{dkd,dot}/res32x4_res8x4.yaml,
+    defaults from mdistiller/engine/cfg.py:50-59,82-86,184-194)."""
+    imagenet = workload.startswith("imagenet")
+    ns = SimpleNamespace
+    return ns(
+        EXPERIMENT=ns(AMP=False),
+        DISTILLER=ns(TYPE=WORKLOADS[workload][5]),
+        DKD=ns(CE_WEIGHT=1.0, ALPHA=1.0, BETA=0.5 if imagenet else 8.0, T=1.0 if imagenet else 4.0,
+               WARMUP=1 if imagenet else 20),
+        KD=ns(TEMPERATURE=1 if imagenet else 4,
+              LOSS=ns(CE_WEIGHT=0.5 if imagenet else 0.1, KD_WEIGHT=0.5 if imagenet else 0.9)),
+        SOLVER=ns(TRAINER=WORKLOADS[workload][6], TYPE="SGD", LR=0.2 if imagenet else 0.05,
+                  WEIGHT_DECAY=1e-4 if imagenet else 5e-4, GRAD_CLIP=0.0,
+                  SGD=ns(MOMENTUM=0.9), DOT=ns(DELTA=0.09 if imagenet else 0.075)),
+    )
+
+
+def build_pair(workload: str, seed: int = 0):
+    teacher_name, student_name, builder, hw, classes = WORKLOADS[workload][:5]
+    torch.manual_seed(seed)
+    teacher = builder(teacher_name, classes)
+    student = builder(student_name, classes)
+    return teacher, student, hw, classes
+
+
+def synthetic_batch(batch: int, hw: int, classes: int, seed: int, device="cpu", pin: bool = False):
+    """(image, target, index) like the reference's train batches (dataset/cifar100.py:14-19)."""
+    g = torch.Generator(device="cpu")
+    g.manual_seed(seed)
+    image = torch.randn(batch, 3, hw, hw, generator=g)
+    target = torch.randint(0, classes, (batch,), generator=g)
+    index = torch.arange(batch)
+    if pin:
+        image, target, index = image.pin_memory(), target.pin_memory(), index.pin_memory()
+    if str(device) != "cpu":
+        image, target, index = image.to(device), target.to(device), index.to(device)
+    return image, target, index

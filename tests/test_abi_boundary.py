@@ -1,0 +1,85 @@
+"""The C-ABI library loads and exports every symbol the header declares (no GPU needed)."""
+
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    names = []
+    inc = os.path.join(ROOT, "include")
+    for f in sorted(os.listdir(inc)):
+        if f.endswith(".h"):
+            text = open(os.path.join(inc, f)).read()
+            names += re.findall(r"MDB200_API\s+[\w\s\*]+?\b(mdb200_\w+)\s*\(", text)
+    return names
+
+
+@pytest.fixture(scope="module")
+def lib():
+    import mdistiller_ddp_b200 as b200
+    b200.build_library()
+    from mdistiller_ddp_b200 import _lib
+    return _lib.load()
+
+
+def test_header_declares_the_expected_surface():
+    assert set(_declared()) >= {"mdb200_abi_version", "mdb200_error_string", "mdb200_loss_workspace_bytes",
+                                "mdb200_distill_loss", "mdb200_scale_by_device_scalar", "mdb200_dot_step",
+                                "mdb200_sgd_step"}
+
+
+def test_every_declared_symbol_is_exported_and_bound(lib):
+    from mdistiller_ddp_b200 import _lib
+    for name in _declared():
+        assert hasattr(lib, name), f"{name} declared in include/*.h but not exported"
+        assert name in _lib.SIGNATURES, f"{name} has no ctypes signature"
+
+
+def test_version_and_error_strings(lib):
+    assert lib.mdb200_abi_version() == 1
+    assert lib.mdb200_error_string(0) == b"ok"
+    assert b"workspace" in lib.mdb200_error_string(-3)
+    assert lib.mdb200_loss_workspace_bytes() >= 64 + 2 * 8 * 1184
+
+
+def test_argument_errors_are_reported_before_any_cuda_work(lib):
+    """Null pointers / bad modes are rejected with the documented codes (no device touched)."""
+    rc = lib.mdb200_distill_loss(None, None, None, 4, 8, 8, 8, 0, 1.0, 1.0, 1.0, 1.0, 0, 1.0,
+                                 None, None, 8, None, None, 0, None)
+    assert rc == -1
+    buf = (ctypes.c_float * 64)()
+    p = ctypes.addressof(buf)
+    rc = lib.mdb200_distill_loss(p, p, p, 4, 8, 4, 8, 0, 1.0, 1.0, 1.0, 1.0, 0, 1.0, p, None, 8, p, p, 1 << 20, None)
+    assert rc == -2          # ld_s < classes
+    rc = lib.mdb200_distill_loss(p, p, p, 4, 8, 8, 8, 0, 1.0, 1.0, 1.0, 1.0, 0, 1.0, p, None, 8, p, p, 16, None)
+    assert rc == -3          # workspace too small
+    rc = lib.mdb200_distill_loss(p, p, p, 4, 8, 8, 8, 7, 1.0, 1.0, 1.0, 1.0, 0, 1.0, p, None, 8, p, p, 1 << 20, None)
+    assert rc == -1          # unknown loss kind
+    assert lib.mdb200_dot_step(None, None, None, None, None, 16, .1, .9, .9, 0., 0., 1., 0, 0, 0, None) == -1
+    assert lib.mdb200_dot_step(p, p, p, p, p, 16, .1, .9, .9, 0., 0., 1., 0, 0, 9, None) == -1
+    assert lib.mdb200_dot_step(p, p, p, p, p, 0, .1, .9, .9, 0., 0., 1., 0, 0, 0, None) == 0   # empty range
+    assert lib.mdb200_sgd_step(p, p, None, 16, .1, .9, 0., 0., 1., 0, None) == -1            # momentum needs v
+
+
+def test_ops_refuse_cpu_tensors():
+    import torch
+    from mdistiller_ddp_b200 import ops
+    z = torch.zeros(4, 8)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.distill_loss(z, z, torch.zeros(4, dtype=torch.long), kind=ops.LOSS_DKD)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.dot_step(torch.zeros(8), torch.zeros(8), torch.zeros(8), torch.zeros(8), torch.zeros(8),
+                     lr=.1, momentum=.9, momentum_kd=.9)
+
+
+def test_missing_library_fails_loudly(monkeypatch, tmp_path):
+    from mdistiller_ddp_b200 import _lib
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_lib, "LIB_PATH", str(tmp_path / "nope.so"))
+    with pytest.raises(_lib.KernelLibraryError, match="no CPU/PyTorch fallback"):
+        _lib.load()

@@ -1,0 +1,165 @@
+"""Parity of the DOT / SGD flat update kernels and of the optimizer built on them -- B200 only.
+
+Bar (BASELINE.json north_star): parameters after 100 DOT steps within rel 1e-5 of the
+reference, rel = max|a-b| / max|b| per tensor.  Calls go through the C-ABI.
+"""
+
+import numpy as np
+import pytest
+import torch
+
+import _cases
+import oracle
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def b200():
+    import mdistiller_ddp_b200 as m
+    return m
+
+
+def _flat(ts, like):
+    return torch.cat([(torch.zeros_like(l) if t is None else t.detach()).reshape(-1)
+                      for t, l in zip(ts, like)]).double().cpu().numpy()
+
+
+def _ref(G, name, key, arr):
+    if f"{name}/{key}" in G:
+        return arr, G[f"{name}/{key}"]
+    return arr[_cases.sample_index(arr.size)], G[f"{name}/{key}_s"]
+
+
+@pytest.mark.parametrize("case", [c for c in _cases.DOT_CASES if c.kind == "dot"], ids=lambda c: c.name)
+def test_100_step_trajectory_matches_reference(case, dot_golden, b200):
+    params = [torch.nn.Parameter(p.clone().cuda()) for p in _cases.make_params(case)]
+    opt = b200.DistillationOrientedTrainer(params, lr=case.lr, momentum=case.momentum - case.delta,
+                                           momentum_kd=case.momentum + case.delta, dampening=case.dampening,
+                                           weight_decay=case.wd)
+    shapes = [p.shape for p in params]
+    for step in range(case.steps):
+        if step == case.lr_drop_at:
+            opt.param_groups[0]["lr"] = case.lr * 0.1       # what adjust_learning_rate does (engine/utils.py:91-92)
+        kd, task = _cases.make_grads(case, step, shapes)
+        opt.zero_grad(set_to_none=True)
+        for p, g in zip(params, kd):
+            p.grad = None if g is None else g.cuda()
+        opt.step_kd()
+        opt.zero_grad(set_to_none=True)
+        for p, g in zip(params, task):
+            p.grad = None if g is None else g.cuda()
+        opt.step()
+    vt, vk = opt.momentum_views()
+    for key, arr in (("p", _flat(params, params)), ("vt", _flat(vt, params)), ("vk", _flat(vk, params))):
+        for tag in ("64", "32"):
+            got, ref = _ref(dot_golden, case.name, key + tag, arr)
+            assert oracle.max_rel_err(got, ref) <= TOL, (case.name, key, tag)
+
+
+@pytest.mark.parametrize("case", [c for c in _cases.DOT_CASES if c.kind == "sgd"], ids=lambda c: c.name)
+def test_sgd_trajectory_matches_torch_sgd(case, dot_golden, b200):
+    params = [torch.nn.Parameter(p.clone().cuda()) for p in _cases.make_params(case)]
+    opt = b200.FlatSGD(params, lr=case.lr, momentum=case.momentum, weight_decay=case.wd, dampening=case.dampening)
+    shapes = [p.shape for p in params]
+    for step in range(case.steps):
+        if step == case.lr_drop_at:
+            opt.param_groups[0]["lr"] = case.lr * 0.1
+        _, task = _cases.make_grads(case, step, shapes)
+        opt.zero_grad()
+        for p, g in zip(params, task):
+            p.grad = g.cuda()
+        opt.step()
+    got, ref = _ref(dot_golden, case.name, "p64", _flat(params, params))
+    assert oracle.max_rel_err(got, ref) <= TOL
+
+
+@pytest.mark.parametrize("n", [11_689_512, 25_557_032, 1_000_003, 5])
+def test_one_step_equals_flat_oracle_at_benchmark_sizes(n, b200):
+    """ResNet18 / ResNet50 element counts (BASELINE.json configs[4]) plus ragged sizes; later
+    steps and the first step; exact up to one rounding of the fused forms."""
+    ops = b200.ops
+    g = torch.Generator().manual_seed(n)
+    p = torch.randn(n, generator=g) * 0.1
+    gt, gk = torch.randn(n, generator=g) * 0.1, torch.randn(n, generator=g) * 0.1
+    vt, vk = torch.randn(n, generator=g) * 0.1, torch.randn(n, generator=g) * 0.1
+    hp = dict(lr=0.2, m_task=0.81, m_kd=0.99, weight_decay=1e-4, dampening=0.0)
+    for first in (False, True):
+        P, VT, VK = p.clone(), vt.clone(), vk.clone()
+        oracle.dot_flat_step(P, gt, gk, VT, VK, first_step=first, **hp)
+        dp, dvt, dvk = p.cuda(), vt.cuda(), vk.cuda()
+        ops.dot_step(dp, gt.cuda(), gk.cuda(), dvt, dvk, lr=0.2, momentum=0.81, momentum_kd=0.99,
+                     weight_decay=1e-4, first_task=first, first_kd=first)
+        for a, b in ((dp, P), (dvt, VT), (dvk, VK)):
+            assert oracle.max_rel_err(a, b) <= 2e-7
+    # unaligned base pointer (scalar path) and the reduce-scatter scale
+    P, VT, VK = p[1:].clone(), vt[1:].clone(), vk[1:].clone()
+    oracle.dot_flat_step(P, gt[1:], gk[1:], VT, VK, grad_scale=0.125, **hp)
+    dp, dvt, dvk = p.cuda(), vt.cuda(), vk.cuda()
+    ops.dot_step(dp[1:], gt.cuda()[1:], gk.cuda()[1:], dvt[1:], dvk[1:], lr=0.2, momentum=0.81, momentum_kd=0.99,
+                 weight_decay=1e-4, grad_scale=0.125)
+    assert oracle.max_rel_err(dp[1:], P) <= 2e-7 and dp[0].item() == p[0].item()
+    # single-momentum SGD mode
+    P, V = p.clone(), vt.clone()
+    oracle.sgd_flat_step(P, gt, V, lr=0.05, momentum=0.9, weight_decay=5e-4)
+    dp, dv = p.cuda(), vt.cuda()
+    ops.sgd_step(dp, gt.cuda(), dv, lr=0.05, momentum=0.9, weight_decay=5e-4)
+    assert oracle.max_rel_err(dp, P) <= 2e-7 and oracle.max_rel_err(dv, V) <= 2e-7
+
+
+def test_update_is_linear_in_lr_and_idempotent_at_zero(b200):
+    """Size-independent properties at the ResNet-50 size: lr = 0 leaves p untouched but advances
+    the momenta; a zero gradient with zero momentum and no decay is the identity."""
+    ops = b200.ops
+    n = 25_557_032
+    p = torch.randn(n, device="cuda") * 0.1
+    g1, g2 = torch.randn(n, device="cuda"), torch.randn(n, device="cuda")
+    vt, vk = torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    p0 = p.clone()
+    ops.dot_step(p, g1, g2, vt, vk, lr=0.0, momentum=0.8, momentum_kd=0.9, weight_decay=0.0)
+    assert torch.equal(p, p0) and torch.equal(vt, g1) and torch.equal(vk, g2)
+    z = torch.zeros(n, device="cuda")
+    vt.zero_(); vk.zero_()
+    ops.dot_step(p, z, z, vt, vk, lr=0.3, momentum=0.8, momentum_kd=0.9, weight_decay=0.0)
+    assert torch.equal(p, p0) and vt.abs().max().item() == 0.0
+
+
+def test_trainer_step_matches_cpu_oracle_end_to_end(b200):
+    """forward -> fused tail -> two backwards -> DOT step on a tiny net, against the same net on the
+    CPU driven by the oracle loss + oracle optimizer (what the reference's DOT.train_iter computes)."""
+    from mdistiller_ddp_b200 import workloads as W
+    import copy
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(0)
+    teacher, student = W.TinyNet(100, 24), W.TinyNet(100, 16)
+    cpu_t, cpu_s = copy.deepcopy(teacher), copy.deepcopy(student)
+    cfg = W.default_cfg("cifar_res32x4_res8x4_kd_dot")
+    cfg.DISTILLER.TYPE = "DKD"
+    dist_gpu = b200.DKD(student, teacher, cfg).cuda().train()
+    tr = b200.StandaloneTrainer(dist_gpu, cfg, kind="dot")
+    cpu_t.eval(); cpu_s.train()
+    cpu_params = [p for _, p in cpu_s.named_parameters()]
+    ref_opt = oracle.DotListOracle([p.data for p in cpu_params], lr=cfg.SOLVER.LR,
+                                   momentum=cfg.SOLVER.SGD.MOMENTUM - cfg.SOLVER.DOT.DELTA,
+                                   momentum_kd=cfg.SOLVER.SGD.MOMENTUM + cfg.SOLVER.DOT.DELTA,
+                                   weight_decay=cfg.SOLVER.WEIGHT_DECAY)
+    for step in range(4):
+        image, target, _ = W.synthetic_batch(32, 32, 100, seed=step)
+        epoch = 5
+        preds, losses = tr.tail_step(image.cuda(), target.cuda(), epoch)
+        zs, _ = cpu_s(image)
+        with torch.no_grad():
+            zt, _ = cpu_t(image)
+        l_ce = cfg.DKD.CE_WEIGHT * oracle.ce_loss(zs, target)
+        l_kd = min(epoch / cfg.DKD.WARMUP, 1.0) * oracle.dkd_loss(zs, zt, target, cfg.DKD.ALPHA, cfg.DKD.BETA, cfg.DKD.T)
+        g_kd = torch.autograd.grad(l_kd, cpu_params, retain_graph=True, allow_unused=True)
+        g_ce = torch.autograd.grad(l_ce, cpu_params, allow_unused=True)
+        ref_opt.step_kd(list(g_kd))
+        ref_opt.step(list(g_ce))
+        assert abs(losses["loss_kd"].item() - l_kd.item()) <= 1e-4 * abs(l_kd.item())
+        assert abs(losses["loss_ce"].item() - l_ce.item()) <= 1e-4 * abs(l_ce.item())
+    for (name, p), q in zip(student.named_parameters(), cpu_params):
+        assert oracle.max_rel_err(p, q) <= 1e-4, name     # cuDNN vs CPU conv rounding dominates here

@@ -1,0 +1,185 @@
+"""Parity of the fused loss kernel with the reference (fixtures) and the oracle -- B200 only.
+
+Every call goes through the C-ABI (`mdistiller_ddp_b200.ops` is a ctypes shim).
+Tolerance (BASELINE.json north_star): loss and d loss/d logits within rel 1e-5 in fp32,
+"rel" = max|a-b| / max|b| per tensor, against the reference's fp64
+output so that the reference's own fp32 rounding is not counted against us.
+"""
+
+import numpy as np
+import pytest
+import torch
+
+import _cases
+import oracle
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from mdistiller_ddp_b200 import ops as _ops
+    return _ops
+
+
+def _grad_err(got: torch.Tensor, G, name, key, n):
+    got = got.detach().double().cpu().numpy()
+    scale = float(G[f"{name}/g{key}_max64"])
+    if f"{name}/g{key}64" in G:
+        ref = G[f"{name}/g{key}64"]
+    else:
+        ref = G[f"{name}/g{key}64_s"]
+        got = got.reshape(-1)[_cases.sample_index(n)]
+    return float(np.abs(got - ref).max() / scale)
+
+
+@pytest.mark.parametrize("case", _cases.LOSS_CASES, ids=lambda c: c.name)
+def test_loss_and_gradient_match_reference_fixture(case, loss_golden, ops):
+    G = loss_golden
+    zs, zt, y = _cases.make_logits(case)
+    np.testing.assert_allclose(_cases.input_checksum(zs, zt, y), G[f"{case.name}/chk"], rtol=0, atol=1e-9)
+    zs, zt, y = zs.cuda(), zt.cuda(), y.cuda()
+    n = case.B * case.C
+    for kind, key in ((ops.LOSS_DKD, "dkd"), (ops.LOSS_KD, "kd")):
+        ref_l = float(G[f"{case.name}/{key}64"])
+        ref_ce = float(G[f"{case.name}/ce64"])
+        # distillation term alone (the dkd_loss / kd_loss functions)
+        lp, g, _ = ops.distill_loss(zs, zt, y, kind=kind, alpha=case.alpha, beta=case.beta, temperature=case.T)
+        assert abs(lp[0].item() - ref_l) <= TOL * abs(ref_l), (key, lp[0].item(), ref_l)
+        assert _grad_err(g, G, case.name, key, n) <= TOL
+        # + cross entropy, separate gradient buffers (DOT trainer)
+        lp, g, gce = ops.distill_loss(zs, zt, y, kind=kind, alpha=case.alpha, beta=case.beta, temperature=case.T,
+                                      ce_mode=ops.CE_SPLIT)
+        assert abs(lp[0].item() - ref_l) <= TOL * abs(ref_l)
+        assert abs(lp[1].item() - ref_ce) <= TOL * abs(ref_ce), (lp[1].item(), ref_ce)
+        assert _grad_err(g, G, case.name, key, n) <= TOL
+        assert _grad_err(gce, G, case.name, "ce", n) <= TOL
+        # + cross entropy summed into one buffer (base trainer), with outer weights
+        lp2, gsum, _ = ops.distill_loss(zs, zt, y, kind=kind, alpha=case.alpha, beta=case.beta, temperature=case.T,
+                                        kd_scale=0.75, ce_mode=ops.CE_COMBINED, ce_scale=0.5)
+        want = 0.75 * g + 0.5 * gce
+        assert oracle.max_rel_err(gsum, want) <= 2e-6
+        assert abs(lp2[0].item() - 0.75 * ref_l) <= TOL * abs(ref_l)
+        assert abs(lp2[1].item() - 0.5 * ref_ce) <= TOL * abs(ref_ce)
+
+
+@pytest.mark.parametrize("shape", [(64, 100), (256, 1000), (100, 40), (17, 512), (9, 2048), (6, 333), (5, 5000)])
+@pytest.mark.parametrize("T", [1.0, 4.0])
+def test_against_live_oracle_on_fresh_seeds(shape, T, ops):
+    """Seeds that are in no fixture; oracle = fp64 closed forms (pinned to the reference on CPU)."""
+    B, C = shape
+    g = torch.Generator().manual_seed(B * 7919 + C)
+    zs = torch.randn(B, C, generator=g) * 3
+    zt = torch.randn(B, C, generator=g) * 3
+    y = torch.randint(0, C, (B,), generator=g)
+    l_dkd, g_dkd = oracle.dkd_closed_form(zs.numpy(), zt.numpy(), y.numpy(), 1.0, 8.0, T)
+    l_kd, g_kd = oracle.kd_closed_form(zs.numpy(), zt.numpy(), T)
+    l_ce, g_ce = oracle.ce_closed_form(zs.numpy(), y.numpy())
+    zs, zt, y = zs.cuda(), zt.cuda(), y.cuda()
+    lp, gk, gc = ops.distill_loss(zs, zt, y, kind=ops.LOSS_DKD, alpha=1.0, beta=8.0, temperature=T,
+                                  ce_mode=ops.CE_SPLIT)
+    assert abs(lp[0].item() - l_dkd) <= TOL * abs(l_dkd) and abs(lp[1].item() - l_ce) <= TOL * abs(l_ce)
+    assert oracle.max_rel_err(gk, g_dkd) <= TOL and oracle.max_rel_err(gc, g_ce) <= TOL
+    lp, gk, gc = ops.distill_loss(zs, zt, y, kind=ops.LOSS_KD, temperature=T, ce_mode=ops.CE_SPLIT)
+    assert abs(lp[0].item() - l_kd) <= TOL * abs(l_kd) and abs(lp[1].item() - l_ce) <= TOL * abs(l_ce)
+    assert oracle.max_rel_err(gk, g_kd) <= TOL and oracle.max_rel_err(gc, g_ce) <= TOL
+
+
+def test_strided_rows_and_unaligned_views(ops):
+    """Logits that are column slices of wider buffers (ld > classes) and a misaligned base."""
+    torch.manual_seed(3)
+    wide_s, wide_t = torch.randn(32, 136, device="cuda") * 3, torch.randn(32, 136, device="cuda") * 3
+    y = torch.randint(0, 100, (32,), device="cuda")
+    for lo in (0, 4, 3):   # 3 -> base pointer not 16-byte aligned -> generic kernel
+        zs, zt = wide_s[:, lo:lo + 100], wide_t[:, lo:lo + 100]
+        lp, g, _ = ops.distill_loss(zs, zt, y, kind=ops.LOSS_DKD, alpha=1.0, beta=8.0, temperature=4.0)
+        l_ref, g_ref = oracle.dkd_closed_form(zs.cpu().numpy(), zt.cpu().numpy(), y.cpu().numpy(), 1.0, 8.0, 4.0)
+        assert abs(lp[0].item() - l_ref) <= TOL * abs(l_ref)
+        assert oracle.max_rel_err(g, g_ref) <= TOL
+
+
+def test_degenerate_rows_stay_finite(ops):
+    """Where the reference's torch.log(0) yields inf/nan the kernel stays finite."""
+    zs = torch.zeros(4, 100, device="cuda")
+    zt = torch.zeros(4, 100, device="cuda")
+    y = torch.tensor([0, 1, 2, 3], device="cuda")
+    zs[0, 0] = 400.0      # student certain of the label: 1 - pi underflows
+    zt[1, 1] = 400.0      # teacher certain
+    zs[2, 5] = 400.0      # student certain of a wrong class
+    lp, g, gc = ops.distill_loss(zs, zt, y, kind=ops.LOSS_DKD, alpha=1.0, beta=8.0, temperature=1.0,
+                                 ce_mode=ops.CE_SPLIT)
+    assert torch.isfinite(lp).all() and torch.isfinite(g).all() and torch.isfinite(gc).all()
+
+
+def test_full_size_properties_65536x1000(ops):
+    """BASELINE.json sweep size: properties that need no CPU oracle at this size."""
+    B, C = 65536, 1000
+    g = torch.Generator(device="cuda").manual_seed(0)
+    zs = torch.randn(B, C, device="cuda", generator=g) * 3
+    zt = torch.randn(B, C, device="cuda", generator=g) * 3
+    y = torch.randint(0, C, (B,), device="cuda", generator=g)
+    lp, gk, gc = ops.distill_loss(zs, zt, y, kind=ops.LOSS_DKD, alpha=1.0, beta=0.5, temperature=1.0,
+                                  ce_mode=ops.CE_SPLIT)
+    # (1) bit-reproducible
+    lp2, gk2, gc2 = ops.distill_loss(zs, zt, y, kind=ops.LOSS_DKD, alpha=1.0, beta=0.5, temperature=1.0,
+                                     ce_mode=ops.CE_SPLIT)
+    assert torch.equal(lp, lp2) and torch.equal(gk, gk2) and torch.equal(gc, gc2)
+    # (2) every gradient row sums to zero (softmax-type gradients), relative to the row's mass
+    for gr in (gk, gc):
+        rs = gr.double().sum(1).abs().max().item()
+        assert rs <= 1e-5 * gr.double().abs().sum(1).max().item()
+    # (3) a CPU-sized slice of rows agrees with the oracle once the 1/B prefactor is accounted for
+    sl = slice(12345, 12345 + 512)
+    l_ref, g_ref = oracle.dkd_closed_form(zs[sl].cpu().numpy(), zt[sl].cpu().numpy(), y[sl].cpu().numpy(), 1.0, 0.5, 1.0)
+    assert oracle.max_rel_err(gk[sl] * (B / 512), g_ref) <= TOL
+    # (4) the batch loss is the mean of the chunk losses (checksum of checksums)
+    chunks = []
+    for i in range(0, B, 16384):
+        l, _, _ = ops.distill_loss(zs[i:i + 16384], zt[i:i + 16384], y[i:i + 16384], kind=ops.LOSS_DKD,
+                                   alpha=1.0, beta=0.5, temperature=1.0, ce_mode=ops.CE_SPLIT)
+        chunks.append(l.double())
+    mean = torch.stack(chunks).mean(0)
+    assert torch.allclose(mean, lp.double(), rtol=2e-6, atol=0)
+    # (5) identical nets: zero loss, zero gradient
+    l0, g0, _ = ops.distill_loss(zs, zs, y, kind=ops.LOSS_KD, temperature=4.0)
+    assert abs(l0[0].item()) <= 1e-6 and g0.abs().max().item() <= 1e-9
+    # (6) shift invariance: adding a per-row constant to the student logits changes nothing
+    shift = torch.randn(B, 1, device="cuda") * 5
+    l3, g3, _ = ops.distill_loss(zs + shift, zt, y, kind=ops.LOSS_DKD, alpha=1.0, beta=0.5, temperature=1.0)
+    assert abs(l3[0].item() - lp[0].item()) <= 1e-5 * abs(lp[0].item())
+    assert oracle.max_rel_err(g3[:4096], gk[:4096]) <= 1e-4   # inputs themselves were rounded by the shift
+
+
+def test_autograd_functions_match_reference_signatures(ops, loss_golden):
+    import mdistiller_ddp_b200 as b200
+    case = _cases.LOSS_CASES[0]
+    zs, zt, y = [t.cuda() for t in _cases.make_logits(case)]
+    a = zs.clone().requires_grad_(True)
+    loss = b200.dkd_loss(a, zt, y, case.alpha, case.beta, case.T)
+    (0.3 * loss).backward()                      # a non-unit upstream gradient, like the warm-up factor
+    ref_l = float(loss_golden[f"{case.name}/dkd64"])
+    assert abs(loss.item() - ref_l) <= TOL * ref_l
+    assert oracle.max_rel_err(a.grad / 0.3, loss_golden[f"{case.name}/gdkd64"]) <= TOL
+    a = zs.clone().requires_grad_(True)
+    loss = b200.kd_loss(a, zt, case.T)
+    loss.backward()
+    assert abs(loss.item() - float(loss_golden[f"{case.name}/kd64"])) <= TOL * loss.item()
+    assert oracle.max_rel_err(a.grad, loss_golden[f"{case.name}/gkd64"]) <= TOL
+    # fused tail: two losses, reference call pattern  kd.backward(retain_graph=True); ce.backward()
+    a = zs.clone().requires_grad_(True)
+    l_kd, l_ce, _ = b200.distill_tail(a, zt, y, kind=ops.LOSS_DKD, alpha=case.alpha, beta=case.beta,
+                                      temperature=case.T, kd_scale=0.5, ce_scale=1.0)
+    l_kd.backward(retain_graph=True)
+    g1 = a.grad.clone()
+    a.grad = None
+    l_ce.backward()
+    assert oracle.max_rel_err(g1 / 0.5, loss_golden[f"{case.name}/gdkd64"]) <= TOL
+    assert oracle.max_rel_err(a.grad, loss_golden[f"{case.name}/gce64"]) <= TOL
+    a = zs.clone().requires_grad_(True)
+    l_kd, l_ce, _ = b200.distill_tail(a, zt, y, kind=ops.LOSS_DKD, alpha=case.alpha, beta=case.beta,
+                                      temperature=case.T)
+    (l_kd + l_ce).backward()
+    want = loss_golden[f"{case.name}/gdkd64"] + loss_golden[f"{case.name}/gce64"]
+    assert oracle.max_rel_err(a.grad, want) <= TOL
