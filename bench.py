@@ -181,16 +181,20 @@ class ClockSampler:
 # ------------------------------------------------------------------------------- GPU arm
 
 def kernel_sweep(dev):
-    """Both kernels alone at BASELINE.json's sweep sizes; L2 flushed (256 MB write) between launches."""
+    """Both kernels alone at BASELINE.json's sweep sizes; L2 flushed between launches (see `timed`)."""
     from mdistiller_ddp_b200 import ops
     peak, _ = hbm_peak()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    drain = torch.empty(64 << 20, dtype=torch.float32, device=dev)
     out = {}
 
     def timed(fn, reps=10):
         ts = []
         for i in range(reps + 2):
+            # cold L2: overwrite it (256 MB of writes), then stream 256 MB of reads through it so the
+            # dirty lines are written back BEFORE the timed launch instead of during it
             flush.fill_(i & 0xFF)
+            drain.sum()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
             fn()

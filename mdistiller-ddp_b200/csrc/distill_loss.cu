@@ -53,44 +53,76 @@ struct RowCoef {
 
 // Row-level scalar algebra shared by the register-resident and the generic kernel.
 //   CE: 0 = none, 1 = T == 1 (softmax(z_s) falls out of the student terms), 2 = any T.
+// Every lane of a row group runs this redundantly, so it is kept to a handful of SFU
+// operations: 4 reciprocals, 4 lg2, 2 ex2 (+1/+1 for the general-T cross entropy).  Only the
+// loss VALUE depends on the logarithms; the gradient coefficients use E, Z and the two
+// exponentials alone.
+__device__ __forceinline__ float fast_rcp(float x) { return __fdividef(1.0f, x); }
+
+// log(a) - log(b) given both logs, or log1p((a-b)/b) when a and b are close (the difference
+// `a_minus_b` is supplied separately because the caller can form it without cancellation).
+__device__ __forceinline__ float log_ratio(float log_a, float log_b, float a_minus_b, float b, float rb) {
+    const float x = a_minus_b * rb;
+    // |x| < 1/8: alternating series of log1p through x^8 (truncation < 1e-8 relative)
+    if (fabsf(a_minus_b) < 0.125f * b) {
+        const float x2 = x * x;
+        float p = fmaf(x, -1.0f / 8.0f, 1.0f / 7.0f);
+        p = fmaf(x, p, -1.0f / 6.0f);
+        p = fmaf(x, p, 1.0f / 5.0f);
+        p = fmaf(x, p, -1.0f / 4.0f);
+        p = fmaf(x, p, 1.0f / 3.0f);
+        p = fmaf(x, p, -0.5f);
+        return fmaf(x2, p, x);
+    }
+    return log_a - log_b;
+}
+
 template <bool DKD, int CE>
 __device__ __forceinline__ RowCoef row_coefficients(const LossArgs &A, float ms, float mt, float Es,
                                                     float Et, float W, float zsg, float ztg, float m1,
                                                     float Z1) {
     RowCoef r;
     r.cce = r.gt_ce = r.loss_ce = 0.f;
-    const float logEs = logf(Es), logEt = logf(Et);
-    const float kl_kept = W * A.inv_t / Et - (logEt - logEs);
+    const float rEs = fast_rcp(Es), rEt = fast_rcp(Et);
+    const float logEs = __logf(Es), logEt = __logf(Et);
+    const float kl_kept = W * A.inv_t * rEt - (logEt - logEs);
     if (DKD) {
+        // label logit relative to the kept-class maximum; exactly one of {a, sh} is 1
         const float dgs = (zsg - ms) * A.inv_t, dgt = (ztg - mt) * A.inv_t;
-        const float hs = fmaxf(dgs, 0.f), ht = fmaxf(dgt, 0.f);
-        const float shs = __expf(-hs), sht = __expf(-ht);
-        const float as = __expf(dgs - hs), bs = Es * shs;
-        const float at = __expf(dgt - ht), bt = Et * sht;
+        const float qs = __expf(-fabsf(dgs)), qt = __expf(-fabsf(dgt));
+        const bool ps = dgs >= 0.f, ptq = dgt >= 0.f;
+        const float as = ps ? 1.f : qs, shs = ps ? qs : 1.f;   // exp(dgs - hs), exp(-hs), hs = max(dgs, 0)
+        const float at = ptq ? 1.f : qt, sht = ptq ? qt : 1.f;
+        const float bs = Es * shs, bt = Et * sht;
         const float Zs = as + bs, Zt = at + bt;
-        const float logZs = logf(Zs), logZt = logf(Zt);
-        const float lpi_s = (dgs - hs) - logZs, lpi_t = (dgt - ht) - logZt;    // log pi
+        const float rZs = fast_rcp(Zs), rZt = fast_rcp(Zt);
+        const float logZs = __logf(Zs), logZt = __logf(Zt);
+        const float hs = fmaxf(dgs, 0.f), ht = fmaxf(dgt, 0.f);
+        const float lpi_s = (dgs - hs) - logZs, lpi_t = (dgt - ht) - logZt;      // log pi
         const float lom_s = (logEs - hs) - logZs, lom_t = (logEt - ht) - logZt;  // log (1 - pi)
-        const float pi_s = as / Zs, pi_t = at / Zt;
-        const float om_s = bs / Zs, om_t = bt / Zt;
-        const float tckd = pi_t * (lpi_t - lpi_s) + om_t * (lom_t - lom_s);
-        r.loss_kd = A.alpha * tckd + A.beta * kl_kept;
+        const float pi_s = as * rZs, pi_t = at * rZt;
+        const float om_s = bs * rZs, om_t = bt * rZt;
         const float d = (pi_s > 0.5f) ? (om_t - om_s) : (pi_s - pi_t);  // pi_s - pi_t without cancellation
-        r.cs = A.c_kd * (A.beta - A.alpha * d) / Es;
-        r.ct = A.c_kd * A.beta / Et;
+        // TCKD = pi_t*log(pi_t/pi_s) + (1-pi_t)*log((1-pi_t)/(1-pi_s)); near-equal arguments go through log1p
+        const float l1 = log_ratio(lpi_t, lpi_s, -d, pi_s, fast_rcp(fmaxf(pi_s, 1e-37f)));
+        const float l2 = log_ratio(lom_t, lom_s, d, om_s, fast_rcp(fmaxf(om_s, 1e-37f)));
+        const float tckd = pi_t * l1 + om_t * l2;
+        r.loss_kd = A.alpha * tckd + A.beta * kl_kept;
+        r.cs = A.c_kd * (A.beta - A.alpha * d) * rEs;
+        r.ct = A.c_kd * A.beta * rEt;
         r.gt_kd = A.c_kd * A.alpha * d;
         if (CE == 1) {
-            r.cce = A.c_ce * shs / Zs;
+            r.cce = A.c_ce * shs * rZs;
             r.gt_ce = -A.c_ce * om_s;
             r.loss_ce = -lpi_s;
         }
     } else {
         r.loss_kd = kl_kept;
-        r.cs = A.c_kd / Es;
-        r.ct = A.c_kd / Et;
+        r.cs = A.c_kd * rEs;
+        r.ct = A.c_kd * rEt;
         r.gt_kd = 0.f;
         if (CE == 1) {
-            r.cce = A.c_ce / Es;
+            r.cce = A.c_ce * rEs;
             r.gt_ce = -A.c_ce;
             r.loss_ce = logEs - (zsg - ms);
         }
@@ -98,9 +130,10 @@ __device__ __forceinline__ RowCoef row_coefficients(const LossArgs &A, float ms,
     if (CE == 2) {
         const float e1g = __expf(zsg - m1);
         const float Zf = DKD ? Z1 + e1g : Z1;  // DKD masked the label out of the register row
-        r.cce = A.c_ce / Zf;
-        r.gt_ce = DKD ? -A.c_ce * (Z1 / Zf) : -A.c_ce;
-        r.loss_ce = logf(Zf) - (zsg - m1);
+        const float rZf = fast_rcp(Zf);
+        r.cce = A.c_ce * rZf;
+        r.gt_ce = DKD ? -A.c_ce * (Z1 * rZf) : -A.c_ce;
+        r.loss_ce = __logf(Zf) - (zsg - m1);
     }
     return r;
 }
