@@ -28,6 +28,8 @@ constexpr int kLossWarps = kLossThreads / 32;
 constexpr int kMaxCtas = 2048;             // partial-sum slots per loss term in the workspace
 constexpr size_t kWorkspaceHeader = 64;    // ticket counter lives here, zero between launches
 constexpr float kNegBig = -1.0e30f;        // padding / masked label: exp2 -> 0, differences stay finite
+// launcher verdict "this grid needs more partial-sum slots than the scratch has" (not a CUDA error)
+constexpr cudaError_t kGridExceedsSlots = static_cast<cudaError_t>(-1000);
 
 struct LossArgs {
     const float *zs, *zt;
@@ -39,7 +41,8 @@ struct LossArgs {
     float c_ce;                    // ce_scale / rows
     double l_kd;                   // kd_scale * T^2 / rows    (loss prefactor)
     double l_ce;                   // ce_scale / rows
-    double *part;                  // [2][kMaxCtas] per-CTA partial sums
+    double *part;                  // [2][slots] per-CTA partial sums
+    int slots;                     // CTA slots per loss term in `part` (kMaxCtas for a caller workspace)
     unsigned *ticket;
     float *loss_out;
 };
@@ -85,7 +88,8 @@ __device__ __forceinline__ RowCoef row_coefficients(const LossArgs &A, float ms,
     r.cce = r.gt_ce = r.loss_ce = 0.f;
     const float rEs = fast_rcp(Es), rEt = fast_rcp(Et);
     const float logEs = __logf(Es), logEt = __logf(Et);
-    const float kl_kept = W * A.inv_t * rEt - (logEt - logEs);
+    // log(Et/Es): series when the two sums are within 12.5 % (small-KL rows), log difference otherwise
+    const float kl_kept = W * A.inv_t * rEt - log_ratio(logEt, logEs, Et - Es, Es, rEs);
     if (DKD) {
         // label logit relative to the kept-class maximum; exactly one of {a, sh} is 1
         const float dgs = (zsg - ms) * A.inv_t, dgt = (ztg - mt) * A.inv_t;
@@ -162,7 +166,7 @@ __device__ __forceinline__ void publish_loss(const LossArgs &A, double cta_kd, d
     __shared__ bool is_last;
     if (threadIdx.x == 0) {
         A.part[blockIdx.x] = cta_kd;
-        A.part[kMaxCtas + blockIdx.x] = cta_ce;
+        A.part[A.slots + blockIdx.x] = cta_ce;
         __threadfence();
         const unsigned t = atomicAdd(A.ticket, 1u);
         is_last = (t == gridDim.x - 1);
@@ -173,7 +177,7 @@ __device__ __forceinline__ void publish_loss(const LossArgs &A, double cta_kd, d
     double s_kd = 0.0, s_ce = 0.0;
     for (unsigned i = threadIdx.x; i < gridDim.x; i += 32) {
         s_kd += __ldcg(A.part + i);
-        s_ce += __ldcg(A.part + kMaxCtas + i);
+        s_ce += __ldcg(A.part + A.slots + i);
     }
     s_kd = warp_sum(s_kd);
     s_ce = warp_sum(s_ce);
@@ -453,6 +457,7 @@ static cudaError_t launch_regs(const LossArgs &A, int sms, cudaStream_t st) {
     const long long cap = (long long)sms * (NV >= 16 ? 2 : (NV >= 8 ? 4 : 8));
     if (want > cap) want = cap;
     if (want > kMaxCtas) want = kMaxCtas;
+    if (want > A.slots) return kGridExceedsSlots;
     loss_rows_in_registers<LPR, NV, DKD, CE, SPLIT><<<(unsigned)want, kLossThreads, 0, st>>>(A);
     return cudaGetLastError();
 }
@@ -470,6 +475,7 @@ static cudaError_t launch_shape(const LossArgs &A, bool vec_ok, int sms, cudaStr
     const long long cap = (long long)sms * 8;
     if (want > cap) want = cap;
     if (want > kMaxCtas) want = kMaxCtas;
+    if (want > A.slots) return kGridExceedsSlots;
     loss_rows_generic<DKD, CE, SPLIT><<<(unsigned)want, kLossThreads, 0, st>>>(A);
     return cudaGetLastError();
 }
@@ -491,11 +497,13 @@ extern "C" size_t mdb200_loss_workspace_bytes(void) {
     return kWorkspaceHeader + 2 * (size_t)kMaxCtas * sizeof(double);
 }
 
-extern "C" int mdb200_distill_loss(const float *z_student, const float *z_teacher, const int64_t *target,
-                                   int64_t rows, int64_t classes, int64_t ld_s, int64_t ld_t, int kind,
-                                   float alpha, float beta, float temperature, float kd_scale, int ce_mode,
-                                   float ce_scale, float *grad_kd, float *grad_ce, int64_t ld_g,
-                                   float *loss_out, void *workspace, size_t workspace_bytes, void *stream) {
+// Argument checks and LossArgs set-up shared by the two loss entry points; the scratch
+// pointers are filled in by the caller.
+static int prepare_loss(LossArgs &A, bool &vec_ok, int &ce, bool &split, const float *z_student,
+                        const float *z_teacher, const int64_t *target, int64_t rows, int64_t classes,
+                        int64_t ld_s, int64_t ld_t, int kind, float alpha, float beta, float temperature,
+                        float kd_scale, int ce_mode, float ce_scale, float *grad_kd, float *grad_ce,
+                        int64_t ld_g, float *loss_out) {
     if (!z_student || !z_teacher || !grad_kd || !loss_out) return MDB200_EINVAL;
     if (rows <= 0 || classes <= 0 || !(temperature > 0.f)) return MDB200_EINVAL;
     if (kind != MDB200_LOSS_DKD && kind != MDB200_LOSS_KD) return MDB200_EINVAL;
@@ -504,12 +512,8 @@ extern "C" int mdb200_distill_loss(const float *z_student, const float *z_teache
     if ((kind == MDB200_LOSS_DKD || ce_mode != MDB200_CE_NONE) && !target) return MDB200_EINVAL;
     if (kind == MDB200_LOSS_DKD && classes < 2) return MDB200_EINVAL;
     if (ld_s < classes || ld_t < classes || ld_g < classes) return MDB200_ESHAPE;
-    if (!workspace || workspace_bytes < mdb200_loss_workspace_bytes()) return MDB200_EWORKSPC;
-    if (!aligned4(z_student) || !aligned4(z_teacher) || !aligned4(grad_kd) || (grad_ce && !aligned4(grad_ce)) ||
-        !aligned16(workspace))
+    if (!aligned4(z_student) || !aligned4(z_teacher) || !aligned4(grad_kd) || (grad_ce && !aligned4(grad_ce)))
         return MDB200_EALIGN;
-
-    LossArgs A;
     A.zs = z_student;
     A.zt = z_teacher;
     A.target = reinterpret_cast<const long long *>(target);
@@ -528,15 +532,30 @@ extern "C" int mdb200_distill_loss(const float *z_student, const float *z_teache
     A.c_ce = (float)((double)ce_scale / (double)rows);
     A.l_kd = (double)kd_scale * (double)temperature * (double)temperature / (double)rows;
     A.l_ce = (ce_mode == MDB200_CE_NONE) ? 0.0 : (double)ce_scale / (double)rows;
+    A.loss_out = loss_out;
+    split = ce_mode == MDB200_CE_SPLIT;
+    vec_ok = (classes % 4 == 0) && (ld_s % 4 == 0) && (ld_t % 4 == 0) && (ld_g % 4 == 0) &&
+             aligned16(z_student) && aligned16(z_teacher) && aligned16(grad_kd) && (!split || aligned16(grad_ce));
+    ce = ce_mode == MDB200_CE_NONE ? 0 : (temperature == 1.0f ? 1 : 2);
+    return 0;
+}
+
+extern "C" int mdb200_distill_loss(const float *z_student, const float *z_teacher, const int64_t *target,
+                                   int64_t rows, int64_t classes, int64_t ld_s, int64_t ld_t, int kind,
+                                   float alpha, float beta, float temperature, float kd_scale, int ce_mode,
+                                   float ce_scale, float *grad_kd, float *grad_ce, int64_t ld_g,
+                                   float *loss_out, void *workspace, size_t workspace_bytes, void *stream) {
+    LossArgs A;
+    bool vec_ok, split;
+    int ce;
+    const int rc = prepare_loss(A, vec_ok, ce, split, z_student, z_teacher, target, rows, classes, ld_s, ld_t, kind,
+                                alpha, beta, temperature, kd_scale, ce_mode, ce_scale, grad_kd, grad_ce, ld_g, loss_out);
+    if (rc != 0) return rc;
+    if (!workspace || workspace_bytes < mdb200_loss_workspace_bytes()) return MDB200_EWORKSPC;
+    if (!aligned16(workspace)) return MDB200_EALIGN;
     A.ticket = reinterpret_cast<unsigned *>(workspace);
     A.part = reinterpret_cast<double *>(reinterpret_cast<char *>(workspace) + kWorkspaceHeader);
-    A.loss_out = loss_out;
-
-    const bool split = ce_mode == MDB200_CE_SPLIT;
-    bool vec_ok = (classes % 4 == 0) && (ld_s % 4 == 0) && (ld_t % 4 == 0) && (ld_g % 4 == 0) &&
-                  aligned16(z_student) && aligned16(z_teacher) && aligned16(grad_kd) &&
-                  (!split || aligned16(grad_ce));
-    const int ce = ce_mode == MDB200_CE_NONE ? 0 : (temperature == 1.0f ? 1 : 2);
+    A.slots = kMaxCtas;
     const int sms = sm_count();
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     cudaError_t e = (kind == MDB200_LOSS_DKD) ? launch_ce<true>(A, ce, split, vec_ok, sms, st)
