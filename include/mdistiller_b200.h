@@ -34,6 +34,7 @@ extern "C" {
 #define MDB200_ESHAPE   (-2)   /* leading dimension smaller than the row length      */
 #define MDB200_EWORKSPC (-3)   /* workspace missing or smaller than required         */
 #define MDB200_EALIGN   (-4)   /* pointer not 4-byte aligned                         */
+#define MDB200_ESCRATCH (-5)   /* launch needs more CTA slots than the built-in scratch */
 
 /* loss kinds */
 #define MDB200_LOSS_DKD 0      /* alpha*TCKD + beta*NCKD   (distillers/DKD.py:8-32)  */
@@ -91,6 +92,43 @@ MDB200_API int mdb200_distill_loss(const float *z_student, const float *z_teache
                         float *grad_kd, float *grad_ce, int64_t ld_g,
                         float *loss_out, void *workspace, size_t workspace_bytes,
                         void *stream);
+
+/*
+ * mdb200_distill_loss without a caller workspace.  (No counterpart in the reference: it
+ * exists for hosts of this library that cannot allocate device memory.)
+ *
+ * Same arguments, kernels and results as mdb200_distill_loss, minus `workspace`: the
+ * partial-sum scratch is a fixed array inside the library (64 + 2 * 8 *
+ * MDB200_STATIC_SCRATCH_CTAS bytes = 16 448 bytes, resident on every GPU that loads the
+ * library until the process exits).  The call itself allocates and frees nothing, on the
+ * host or the device, and uses no allocating library routine; inputs and outputs are
+ * still the caller's buffers.
+ *
+ * Limit: the launch may use at most MDB200_STATIC_SCRATCH_CTAS thread blocks.  The grid
+ * is chosen exactly as in mdb200_distill_loss: ceil(rows / R) blocks, capped per SM.
+ * On the 16-byte-friendly path (classes and strides multiples of 4, aligned pointers):
+ *   classes <= 128          R = 32, cap 8/SM  -> on a 148-SM B200 fits up to 32 768 rows
+ *   128 < classes <= 512    R = 8,  cap 8/SM  -> fits up to 8 192 rows
+ *   512 < classes <= 2048   R = 8,  cap 4/SM or 2/SM (592 / 296 blocks) -> always fits
+ * and for every other shape R = 1, cap 8/SM -> fits up to 1 024 rows.  Anything larger is
+ * refused with MDB200_ESCRATCH and nothing is launched; use mdb200_distill_loss there.
+ *
+ * Sharing: all calls on a device use the same array.  The entry point clears the part
+ * that must start at zero on `stream` before the kernel, so back-to-back calls on one
+ * stream are fine; two calls whose kernels can overlap on the GPU (different streams,
+ * no dependency) race on it and must be serialised by the caller.
+ *
+ * First call on each device: resolves the device address of the array
+ * (cudaGetSymbolAddress with that device current) and caches it; make that first call
+ * outside any stream capture.
+ */
+#define MDB200_STATIC_SCRATCH_CTAS 1024
+MDB200_API int mdb200_distill_loss_static_scratch(const float *z_student, const float *z_teacher,
+                        const int64_t *target, int64_t rows, int64_t classes, int64_t ld_s, int64_t ld_t,
+                        int kind, float alpha, float beta, float temperature,
+                        float kd_scale, int ce_mode, float ce_scale,
+                        float *grad_kd, float *grad_ce, int64_t ld_g,
+                        float *loss_out, void *stream);
 
 /*
  * out[i] = grad[i] * (*upstream)   -- the autograd "grad_output" multiply

@@ -30,6 +30,8 @@ SIGNATURES = {
     "mdb200_loss_workspace_bytes": (C.c_size_t, []),
     "mdb200_distill_loss": (_int, [_ptr, _ptr, _ptr, _i64, _i64, _i64, _i64, _int, _f32, _f32, _f32,
                                    _f32, _int, _f32, _ptr, _ptr, _i64, _ptr, _ptr, C.c_size_t, _ptr]),
+    "mdb200_distill_loss_static_scratch": (_int, [_ptr, _ptr, _ptr, _i64, _i64, _i64, _i64, _int, _f32, _f32,
+                                                  _f32, _f32, _int, _f32, _ptr, _ptr, _i64, _ptr, _ptr]),
     "mdb200_scale_by_device_scalar": (_int, [_ptr, _ptr, _ptr, _i64, _ptr]),
     "mdb200_dot_step": (_int, [_ptr, _ptr, _ptr, _ptr, _ptr, _i64, _f32, _f32, _f32, _f32, _f32, _f32,
                                _int, _int, _int, _ptr]),

@@ -19,6 +19,8 @@
 // cat_mask does and what keeps (1 - pi) accurate for confident rows (Appendix A.4).
 // Everything stays finite where the reference's torch.log(0) would give inf/nan.
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace mdb200 {
@@ -560,6 +562,75 @@ extern "C" int mdb200_distill_loss(const float *z_student, const float *z_teache
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     cudaError_t e = (kind == MDB200_LOSS_DKD) ? launch_ce<true>(A, ce, split, vec_ok, sms, st)
                                               : launch_ce<false>(A, ce, split, vec_ok, sms, st);
+    return (int)e;
+}
+
+// ---------------------------------------------------------------------------------------
+// Allocation-free variant: the reduction scratch lives inside the library image.
+//
+// Some hosts of this library are handed device pointers by another runtime and own no
+// allocator of their own: a custom-call plugin inside a framework that has reserved all of
+// HBM for its arena, or a latency-sensitive thread that must not issue cudaMalloc because
+// it serialises against every stream on the device.  They cannot produce the workspace the
+// regular entry point asks for, so this one brings its own, fixed at build time.
+//
+// The array below is a DEVICE object; in host code its name is only a handle for
+// cudaGetSymbolAddress (passing `g_static_scratch` itself to a kernel would hand it a host
+// address).  Each device that runs this entry point resolves its own copy once.
+// ---------------------------------------------------------------------------------------
+constexpr int kStaticSlots = MDB200_STATIC_SCRATCH_CTAS;
+constexpr size_t kStaticScratchBytes = kWorkspaceHeader + 2 * (size_t)kStaticSlots * sizeof(double);
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+constexpr int kMaxDevices = 64;
+static void *s_static_scratch_ptr[kMaxDevices];   // per-device address of g_static_scratch, 0 = not resolved yet
+static std::mutex s_static_scratch_mutex;
+
+// Device address of this device's copy of the scratch (resolved on first use, then cached).
+static int static_scratch_for_current_device(void **out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= kMaxDevices) return MDB200_EINVAL;
+    std::lock_guard<std::mutex> lock(s_static_scratch_mutex);
+    if (s_static_scratch_ptr[dev] == nullptr) {
+        void *ptr = nullptr;
+        e = cudaGetSymbolAddress((void **)&ptr, g_static_scratch);   // `dev` is current here
+        if (e != cudaSuccess) return (int)e;
+        if (ptr == nullptr) return (int)cudaErrorInvalidSymbol;
+        s_static_scratch_ptr[dev] = ptr;
+    }
+    *out = s_static_scratch_ptr[dev];
+    return 0;
+}
+
+extern "C" int mdb200_distill_loss_static_scratch(const float *z_student, const float *z_teacher,
+                                                  const int64_t *target, int64_t rows, int64_t classes,
+                                                  int64_t ld_s, int64_t ld_t, int kind, float alpha, float beta,
+                                                  float temperature, float kd_scale, int ce_mode, float ce_scale,
+                                                  float *grad_kd, float *grad_ce, int64_t ld_g, float *loss_out,
+                                                  void *stream) {
+    LossArgs A;
+    bool vec_ok, split;
+    int ce;
+    int rc = prepare_loss(A, vec_ok, ce, split, z_student, z_teacher, target, rows, classes, ld_s, ld_t, kind, alpha,
+                          beta, temperature, kd_scale, ce_mode, ce_scale, grad_kd, grad_ce, ld_g, loss_out);
+    if (rc != 0) return rc;
+    void *scratch = nullptr;
+    rc = static_scratch_for_current_device(&scratch);
+    if (rc != 0) return rc;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    // The array keeps whatever the previous call (or an aborted one) left behind; only the
+    // arrival counter in the header has to start at zero, the partial sums are overwritten.
+    cudaError_t e = cudaMemsetAsync(scratch, 0, kWorkspaceHeader, st);
+    if (e != cudaSuccess) return (int)e;
+    A.ticket = reinterpret_cast<unsigned *>(scratch);
+    A.part = reinterpret_cast<double *>(reinterpret_cast<char *>(scratch) + kWorkspaceHeader);
+    A.slots = kStaticSlots;
+    const int sms = sm_count();
+    e = (kind == MDB200_LOSS_DKD) ? launch_ce<true>(A, ce, split, vec_ok, sms, st)
+                                  : launch_ce<false>(A, ce, split, vec_ok, sms, st);
+    if (e == kGridExceedsSlots) return MDB200_ESCRATCH;
     return (int)e;
 }
 

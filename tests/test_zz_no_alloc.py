@@ -1,0 +1,80 @@
+"""The allocation-free loss entry point gives the same answers as the regular one.
+
+`mdb200_distill_loss_static_scratch` is for hosts that cannot allocate device memory (a
+plugin living inside another runtime's pre-reserved arena, or a thread that must not stall
+the device with cudaMalloc): it keeps its partial-sum scratch in a fixed array inside the
+library instead of taking a workspace.  Here it is called straight through the C-ABI,
+twice in a row with different shapes -- so the second call finds the first one's leftovers
+in the shared array -- and each result is compared with `mdb200_distill_loss` on the same
+inputs at the tolerance of the other loss tests (rel 1e-5; in practice the two are
+bit-identical because they run the same kernel with the same grid).  The file sorts last so
+that a `-x` run has already been through every other test; it also passes on its own in a
+fresh process, where its first call is the one that resolves the array's device address.
+"""
+
+import ctypes
+
+import pytest
+import torch
+
+import oracle
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-5
+ESCRATCH = -5
+
+
+def _inputs(rows, classes, seed):
+    g = torch.Generator().manual_seed(seed)
+    zs = (torch.randn(rows, classes, generator=g) * 3).cuda()
+    zt = (torch.randn(rows, classes, generator=g) * 3).cuda()
+    y = torch.randint(0, classes, (rows,), generator=g).cuda()
+    return zs, zt, y
+
+
+def _call_static(lib, zs, zt, y, kind, alpha, beta, T, ce_mode):
+    """Raw C-ABI call: the caller owns inputs and outputs, nothing else is passed."""
+    rows, classes = zs.shape
+    gk, gc = torch.empty_like(zs), torch.empty_like(zs)
+    loss = torch.empty(2, device=zs.device)
+    rc = lib.mdb200_distill_loss_static_scratch(
+        zs.data_ptr(), zt.data_ptr(), y.data_ptr(), rows, classes, zs.stride(0), zt.stride(0),
+        kind, alpha, beta, T, 1.0, ce_mode, 1.0, gk.data_ptr(), gc.data_ptr(), gk.stride(0),
+        loss.data_ptr(), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    return rc, loss, gk, gc
+
+
+def test_static_scratch_entry_point_matches_workspace_entry_point_twice_in_a_row():
+    from mdistiller_ddp_b200 import _lib, ops
+    lib = _lib.load()
+    # two consecutive calls: ImageNet-shaped DKD + split CE, then a CIFAR-shaped KD with T = 4
+    for (rows, classes, kind, beta, T, seed) in ((256, 1000, ops.LOSS_DKD, 0.5, 1.0, 1),
+                                                 (4096, 100, ops.LOSS_KD, 1.0, 4.0, 2)):
+        zs, zt, y = _inputs(rows, classes, seed)
+        rc, loss, gk, gc = _call_static(lib, zs, zt, y, kind, 1.0, beta, T, ops.CE_SPLIT)
+        assert rc == 0, lib.mdb200_error_string(rc)
+        want_loss, want_gk, want_gc = ops.distill_loss(zs, zt, y, kind=kind, alpha=1.0, beta=beta,
+                                                       temperature=T, ce_mode=ops.CE_SPLIT)
+        torch.cuda.synchronize()
+        assert oracle.max_rel_err(loss, want_loss) <= TOL
+        assert oracle.max_rel_err(gk, want_gk) <= TOL
+        assert oracle.max_rel_err(gc, want_gc) <= TOL
+
+
+def test_static_scratch_entry_point_refuses_launches_beyond_its_slots():
+    from mdistiller_ddp_b200 import _lib, ops
+    lib = _lib.load()
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    if sms * 8 <= 1024:
+        pytest.skip("this GPU never needs more than 1024 thread blocks")
+    zs, zt, y = _inputs(40000, 100, 3)          # 1250 blocks wanted, capped at 8 per SM > 1024 slots
+    rc, loss, gk, gc = _call_static(lib, zs, zt, y, ops.LOSS_DKD, 1.0, 8.0, 4.0, ops.CE_NONE)
+    assert rc == ESCRATCH
+    assert b"built-in scratch" in lib.mdb200_error_string(rc)
+    # the refusal launched nothing and left the scratch usable
+    zs, zt, y = _inputs(512, 100, 4)
+    rc, loss, gk, _ = _call_static(lib, zs, zt, y, ops.LOSS_DKD, 1.0, 8.0, 4.0, ops.CE_NONE)
+    assert rc == 0
+    want_loss, want_gk, _ = ops.distill_loss(zs, zt, y, kind=ops.LOSS_DKD, alpha=1.0, beta=8.0, temperature=4.0)
+    assert oracle.max_rel_err(loss[:1], want_loss[:1]) <= TOL and oracle.max_rel_err(gk, want_gk) <= TOL
