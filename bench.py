@@ -61,11 +61,12 @@ def hbm_peak():
         return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def profiled_traffic(kernel: str):
-    """dram bytes per launch from the committed ncu capture, if one has been summarised."""
+def profiled_traffic(kernel: str, n_elements: int):
+    """dram bytes per launch from the committed ncu capture -- only if it was taken at this launch size."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            return json.load(f).get(kernel)
+            rec = json.load(f).get(kernel)
+        return rec["dram_bytes"] if rec and rec.get("n_elements") == n_elements else None
     except Exception:
         return None
 
@@ -366,7 +367,7 @@ def run_b200_arm(args):
         "clocks": clocks,
         "roofline": {"kernel": "flat_step_vec4<true,true> (mdb200_dot_step)", "bound": "hbm",
                      "achieved": dot_bytes / dot_avg / 1e9, "peak": peak, "unit": "GB/s",
-                     "frac": dot_bytes / dot_avg / 1e9 / peak, "traffic": profiled_traffic("dot_step"),
+                     "frac": dot_bytes / dot_avg / 1e9 / peak, "traffic": profiled_traffic("dot_step", shard_elems),
                      "peak_source": peak_src, "bytes_per_launch": dot_bytes, "us_per_launch": dot_avg * 1e6,
                      "launches_timed": len(dot_t),
                      "note": "timed in-step right after backward: part of the 234 MB working set is L2-resident"},

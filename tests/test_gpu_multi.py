@@ -1,0 +1,119 @@
+"""Sharded step over NCCL on real GPUs (needs >= 2 devices; skipped on a 1-GPU box).
+
+Oracle for N > 1: the single-process reference fed rank-averaged gradients.
+"""
+
+import os
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import _cases
+import oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _need_gpus(n):
+    if torch.cuda.device_count() < n:
+        pytest.skip(f"needs {n} GPUs, have {torch.cuda.device_count()}")
+
+
+def _opt_worker(rank, world, port, case_idx, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        import mdistiller_ddp_b200 as b200
+        case = _cases.DOT_CASES[case_idx]
+        params = [torch.nn.Parameter((p.clone() + (0.5 if rank else 0.0)).cuda()) for p in _cases.make_params(case)]
+        opt = b200.DistillationOrientedTrainer(params, lr=case.lr, momentum=case.momentum - case.delta,
+                                               momentum_kd=case.momentum + case.delta, weight_decay=case.wd)
+        assert opt.world_size == world
+        shapes = [p.shape for p in params]
+        # per-rank gradient factors with mean 1 over ranks
+        f_kd = 1.0 + 0.25 * (rank - (world - 1) / 2)
+        f_task = 1.0 - 0.5 * (rank - (world - 1) / 2)
+        for step in range(12):
+            if step == 6:
+                opt.param_groups[0]["lr"] = case.lr * 0.1
+            kd, task = _cases.make_grads(case, step, shapes)
+            opt.zero_grad()
+            for p, g in zip(params, kd):
+                p.grad = None if g is None else (g * f_kd).cuda()
+            opt.step_kd()
+            opt.zero_grad()
+            for p, g in zip(params, task):
+                p.grad = None if g is None else (g * f_task).cuda()
+            opt.step()
+        flat = opt.flat_params.clone()
+        gathered = [torch.empty_like(flat) for _ in range(world)]
+        dist.all_gather(gathered, flat)
+        assert all(torch.equal(g, flat) for g in gathered), "ranks diverged after the all-gather"
+        sd = opt.state_dict()
+        if rank == 0:
+            torch.save({"p": [p.detach().cpu() for p in params],
+                        "state": {k: {n: t.cpu() for n, t in v.items()} for k, v in sd["state"].items()}}, out)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,case_idx", [(2, 0), (2, 2), (4, 6), (8, 6)])
+def test_sharded_dot_step_matches_oracle_on_rank_averaged_gradients(world, case_idx, tmp_path):
+    _need_gpus(world)
+    out = str(tmp_path / "r0.pt")
+    port = 29600 + (os.getpid() % 1500) + world * 3 + case_idx
+    mp.spawn(_opt_worker, args=(world, port, case_idx, out), nprocs=world, join=True)
+    got = torch.load(out, weights_only=False)
+    case = _cases.DOT_CASES[case_idx]
+    params = [p.clone() for p in _cases.make_params(case)]
+    ref = oracle.DotListOracle(params, lr=case.lr, momentum=case.momentum - case.delta,
+                               momentum_kd=case.momentum + case.delta, weight_decay=case.wd)
+    shapes = [p.shape for p in params]
+    for step in range(12):
+        if step == 6:
+            ref.hp["lr"] = case.lr * 0.1
+        kd, task = _cases.make_grads(case, step, shapes)
+        ref.step_kd(kd)
+        ref.step(task)
+    for p, q in zip(got["p"], params):
+        assert oracle.max_rel_err(p, q) <= 1e-5
+    for i in range(len(params)):
+        if ref.buf_kd[i] is not None:
+            assert oracle.max_rel_err(got["state"][i]["momentum_kd_buffer"], ref.buf_kd[i]) <= 1e-5
+        if ref.buf_task[i] is not None:
+            assert oracle.max_rel_err(got["state"][i]["momentum_buffer"], ref.buf_task[i]) <= 1e-5
+
+
+def _trainer_worker(rank, world, port):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), LOCAL_RANK=str(rank), WORLD_SIZE=str(world))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        import mdistiller_ddp_b200 as b200
+        from mdistiller_ddp_b200 import workloads as W
+        from torch.nn.parallel import DistributedDataParallel as DDP
+        torch.manual_seed(0)
+        teacher, student = W.TinyNet(100, 24), W.TinyNet(100, 16)
+        cfg = W.default_cfg("cifar_res32x4_res8x4_kd_dot")
+        distiller = b200.DKD(student, teacher, cfg).cuda().train()
+        wrapped = DDP(distiller, device_ids=[rank], find_unused_parameters=True)   # as tools/train.py:86
+        tr = b200.StandaloneTrainer(wrapped, cfg, kind="dot")
+        meters = b200.new_train_meters()
+        for step in range(3):
+            batch = W.synthetic_batch(16, 32, 100, seed=100 * step + rank)
+            msg = tr.train_iter(batch, 2, meters)
+        flat = tr.optimizer.flat_params
+        other = [torch.empty_like(flat) for _ in range(world)]
+        dist.all_gather(other, flat.clone())
+        assert all(torch.equal(o, flat) for o in other)
+        assert torch.isfinite(flat).all() and meters["top1"].count == 3 * 16 * world, msg
+    finally:
+        dist.destroy_process_group()
+
+
+def test_trainer_under_ddp_wrapper_keeps_ranks_in_sync():
+    _need_gpus(2)
+    mp.spawn(_trainer_worker, args=(2, 29900 + os.getpid() % 90), nprocs=2, join=True)
