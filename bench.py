@@ -47,6 +47,8 @@ def parse():
     ap.add_argument("--workload", default="imagenet_r34_r18_dkd_dot")
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (0 = the workload's)")
     ap.add_argument("--cpu-batch", type=int, default=16, help="bounded CPU sample: images per CPU step")
+    ap.add_argument("--comm", default="nccl", choices=["nccl", "fused", "fused_kd", "fused_p2p", "fused_kd_p2p"],
+                    help="data-parallel step: NCCL launches or the fused NVLink kernel (N > 1)")
     ap.add_argument("--no-sweep", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     return ap.parse_args()
@@ -257,6 +259,7 @@ def run_b200_arm(args):
     teacher, student, hw, classes = W.build_pair(args.workload, seed=0)
     cfg = W.default_cfg(args.workload)
     distiller = b200.distiller_dict[cfg.DISTILLER.TYPE](student, teacher, cfg).to(dev).train()
+    b200.TailStepMixin.comm_mode = args.comm
     trainer = b200.StandaloneTrainer(distiller, cfg)
     n_params = sum(p.numel() for p in distiller.get_learnable_parameters())
     shard_elems = trainer.optimizer._space.shard_len
@@ -268,7 +271,7 @@ def run_b200_arm(args):
     # live timing of our two kernels inside the timed region (events on the launching stream)
     probes = {"dot": [], "loss": []}
     probing = {"on": False}
-    orig_dot, orig_loss = ops.dot_step, ops.distill_loss
+    orig_dot, orig_loss, orig_fused = ops.dot_step, ops.distill_loss, ops.dot_step_fused
 
     def wrap(name, fn):
         def inner(*a, **k):
@@ -282,7 +285,11 @@ def run_b200_arm(args):
             return r
         return inner
 
+    probes["opt_step"] = []
+    opt = trainer.optimizer
+    opt.step = wrap("opt_step", opt.step)
     ops.dot_step = wrap("dot", orig_dot)
+    ops.dot_step_fused = wrap("dot", orig_fused)
     ops.distill_loss = wrap("loss", orig_loss)
     # losses.py / optim.py call through the `ops` module attribute, so the wrappers are seen
 
@@ -341,6 +348,7 @@ def run_b200_arm(args):
     dot_avg = sum(dot_t) / len(dot_t)
     dot_bytes = 32 * shard_elems
     loss_avg = sum(loss_t) / len(loss_t)
+    step_t = [a.elapsed_time(b) * 1e-3 for a, b in probes["opt_step"]]
     loss_bytes = 16 * per_gpu * classes + 8 * per_gpu + 8
 
     if rank != 0:
@@ -356,7 +364,8 @@ def run_b200_arm(args):
         "config": {"workload": f"{args.workload}: DKD+DOT ResNet34->ResNet18, synthetic ImageNet 224x224x3, "
                                f"1000 classes, random-init" if args.workload == "imagenet_r34_r18_dkd_dot" else args.workload,
                    "per_gpu_batch": per_gpu, "global_batch": per_gpu * world, "student_params": n_params,
-                   "parallelism": f"dp{world}: reduce-scatter x2 -> DOT on 1/{world} shard -> all-gather",
+                   "parallelism": (f"dp{world}: reduce-scatter x2 -> DOT on 1/{world} shard -> all-gather (NCCL)" if args.comm == "nccl" or world == 1
+                                   else f"dp{world}: fused NVLink kernel ({args.comm}): in-switch gradient sum -> DOT on 1/{world} shard -> multicast store"),
                    "backbone_math": "fp32 storage, cuDNN TF32 convolutions allowed (torch default, as the reference)",
                    "l2": "inputs_exceed_l2 (154 MB batch, >1 GB activations per step)"},
         "e2e": {"value": world * per_gpu * args.steps / e2e_secs, "unit": UNIT, "h2d_bytes_per_step": h2d,
@@ -364,6 +373,10 @@ def run_b200_arm(args):
                 "api": "StandaloneTrainer.train_iter((image, target, index), epoch, meters) -- the mirror of "
                        "DOT.train_iter (trainer.py:412-461)"},
         "gpu_launches": launches,
+        "optimizer_step": {"us": 1e6 * sum(step_t) / max(1, len(step_t)),
+                           "what": "optimizer.step(): task-bucket collective + DOT kernel + parameter write-back, "
+                                   "CUDA events on the compute stream", "comm": args.comm if world > 1 else "none",
+                           "fused": getattr(trainer.optimizer, "last_fused", None)},
         "clocks": clocks,
         "roofline": {"kernel": "flat_step_vec4<true,true> (mdb200_dot_step)", "bound": "hbm",
                      "achieved": dot_bytes / dot_avg / 1e9, "peak": peak, "unit": "GB/s",

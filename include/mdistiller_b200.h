@@ -105,13 +105,13 @@ MDB200_API int mdb200_distill_loss(const float *z_student, const float *z_teache
  * still the caller's buffers.
  *
  * Limit: the launch may use at most MDB200_STATIC_SCRATCH_CTAS thread blocks.  The grid
- * is chosen exactly as in mdb200_distill_loss: ceil(rows / R) blocks, capped per SM.
- * On the 16-byte-friendly path (classes and strides multiples of 4, aligned pointers):
- *   classes <= 128          R = 32, cap 8/SM  -> on a 148-SM B200 fits up to 32 768 rows
- *   128 < classes <= 512    R = 8,  cap 8/SM  -> fits up to 8 192 rows
- *   512 < classes <= 2048   R = 8,  cap 4/SM or 2/SM (592 / 296 blocks) -> always fits
- * and for every other shape R = 1, cap 8/SM -> fits up to 1 024 rows.  Anything larger is
- * refused with MDB200_ESCRATCH and nothing is launched; use mdb200_distill_loss there.
+ * is chosen exactly as in mdb200_distill_loss: min(ceil(rows / R), SMs x resident blocks
+ * per SM).  On a 148-SM B200 the register-resident kernels (classes and strides multiples
+ * of 4, 16-byte aligned pointers, classes <= 2048) hold at most 4 blocks per SM, i.e. at
+ * most 592 blocks, and always fit.  Shapes outside that path run one row per block with up
+ * to 8 resident blocks per SM (KD) or 4 (DKD): those fit up to 1 024 rows in KD mode and
+ * always in DKD mode.  Anything larger is refused with MDB200_ESCRATCH and nothing is
+ * launched; use mdb200_distill_loss there.
  *
  * Sharing: all calls on a device use the same array.  The entry point clears the part
  * that must start at zero on `stream` before the kernel, so back-to-back calls on one
@@ -158,6 +158,39 @@ MDB200_API int mdb200_dot_step(float *p, const float *g_task, const float *g_kd,
                     float lr, float momentum, float momentum_kd, float weight_decay,
                     float dampening, float grad_scale, int first_task, int first_kd,
                     int membership, void *stream);
+
+/*
+ * Data-parallel DOT step as ONE kernel over NVLink peer memory: gradient sum over ranks ->
+ * dual-momentum update -> parameters written to every rank, for the element range
+ * [shard_lo, shard_lo + shard_len) this rank owns.
+ *
+ * Replaces DDP's bucketed all-reduce (tools/train.py:86) followed by dot()
+ * (mdistiller/engine/dot.py:15-55) on this path, and the NCCL reduce-scatter / all-gather
+ * pair of the unfused step.  Arithmetic is mdb200_dot_step's MDB200_DOT_BOTH case.
+ *
+ *   p_local / g_task_local / g_kd_local   this rank's FULL flat buffers (symmetric allocations:
+ *                                         same size on every rank, mapped into every peer)
+ *   *_multicast                           NVSwitch multicast address of the same buffer, or NULL;
+ *                                         when given, sums use multimem.ld_reduce and the
+ *                                         parameter write-back multimem.st (in-switch, "NVLS")
+ *   *_peers                               host array[world] of every rank's base address of the
+ *                                         buffer (own rank included); used when no multicast
+ *   kd_is_reduced                         non-zero: g_kd_local[shard] already holds the SUM over
+ *                                         ranks (reduce-scattered earlier, e.g. overlapped with
+ *                                         the second backward); only the task gradient is fetched
+ *   v_task, v_kd                          rank-local momentum, shard_len elements
+ *   grad_scale                            normally 1/world
+ * shard_lo and shard_len are multiples of 4; world <= 16.  The caller must order the launch
+ * after every rank's gradients are complete and visible (symmetric-memory barrier) and must
+ * not let any rank read P before every rank's kernel has finished (second barrier).
+ */
+MDB200_API int mdb200_dot_step_fused(float *p_local, float *p_multicast, float *const *p_peers,
+                    const float *g_task_local, const float *g_task_multicast, float *const *g_task_peers,
+                    const float *g_kd_local, const float *g_kd_multicast, float *const *g_kd_peers,
+                    int kd_is_reduced, float *v_task, float *v_kd,
+                    int64_t shard_lo, int64_t shard_len, int world,
+                    float lr, float momentum, float momentum_kd, float weight_decay,
+                    float dampening, float grad_scale, int first_task, int first_kd, void *stream);
 
 /*
  * Single-momentum SGD on a flat range, in place: torch.optim.SGD(momentum,

@@ -35,6 +35,8 @@ SIGNATURES = {
     "mdb200_scale_by_device_scalar": (_int, [_ptr, _ptr, _ptr, _i64, _ptr]),
     "mdb200_dot_step": (_int, [_ptr, _ptr, _ptr, _ptr, _ptr, _i64, _f32, _f32, _f32, _f32, _f32, _f32,
                                _int, _int, _int, _ptr]),
+    "mdb200_dot_step_fused": (_int, [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _int, _ptr, _ptr,
+                                     _i64, _i64, _int, _f32, _f32, _f32, _f32, _f32, _f32, _int, _int, _ptr]),
     "mdb200_sgd_step": (_int, [_ptr, _ptr, _ptr, _i64, _f32, _f32, _f32, _f32, _f32, _int, _ptr]),
 }
 

@@ -57,3 +57,49 @@ class ShardComm:
     def all_reduce_max(self, t: torch.Tensor):
         if self.world_size > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+
+
+class SymmetricShardComm(ShardComm):
+    """Flat buffers in NVLink symmetric memory, so the step can run as ONE fused kernel
+    (`mdb200_dot_step_fused`: in-switch gradient sum -> DOT update -> multicast parameter store)
+    instead of reduce-scatter / update / all-gather launches.
+
+    ``fuse_kd=False`` (default) keeps the KD bucket on an asynchronous NCCL reduce-scatter issued
+    from ``step_kd()`` so that it overlaps the second backward; the fused kernel then pulls only
+    the task bucket through the switch.  ``fuse_kd=True`` pulls both.
+    ``use_multicast=False`` forces plain peer loads/stores even where NVLS is available.
+    """
+
+    fused = True
+
+    def __init__(self, group: Optional[dist.ProcessGroup] = None, fuse_kd: bool = False,
+                 use_multicast: bool = True, barrier_timeout_ms: int = 20000):
+        super().__init__(group)
+        if self.world_size > 16:
+            raise ValueError("the fused kernel addresses at most 16 peers")
+        self.fuse_kd = fuse_kd
+        self.use_multicast = use_multicast
+        self.barrier_timeout_ms = barrier_timeout_ms
+        self._handles = {}
+
+    def alloc_flat(self, n: int, device: torch.device) -> torch.Tensor:
+        """Collective: every rank must allocate the same sequence of buffers."""
+        import torch.distributed._symmetric_memory as symm_mem
+        t = symm_mem.empty(n, dtype=torch.float32, device=device)
+        hdl = symm_mem.rendezvous(t, self.group if self.group is not None else dist.group.WORLD)
+        t.zero_()
+        self._handles[t.data_ptr()] = hdl
+        return t
+
+    def handle(self, t: torch.Tensor):
+        return self._handles[t.data_ptr()]
+
+    def addresses(self, t: torch.Tensor):
+        """(multicast address or 0, [base address on every rank]) of a symmetric flat buffer."""
+        h = self.handle(t)
+        mc = int(h.multicast_ptr) if self.use_multicast else 0
+        return mc, [int(a) for a in h.buffer_ptrs]
+
+    def barrier(self, t: torch.Tensor, channel: int = 0) -> None:
+        """Device-side barrier across ranks on the current stream (signal pad of `t`'s allocation)."""
+        self.handle(t).barrier(channel=channel, timeout_ms=self.barrier_timeout_ms)

@@ -162,32 +162,15 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
-// CTA partials -> workspace; the last CTA to arrive adds them in index order, so the
-// two loss values are reproducible bit for bit (fixed grid => fixed summation tree).
-__device__ __forceinline__ void publish_loss(const LossArgs &A, double cta_kd, double cta_ce) {
-    __shared__ bool is_last;
-    if (threadIdx.x == 0) {
-        A.part[blockIdx.x] = cta_kd;
-        A.part[A.slots + blockIdx.x] = cta_ce;
-        __threadfence();
-        const unsigned t = atomicAdd(A.ticket, 1u);
-        is_last = (t == gridDim.x - 1);
-    }
-    __syncthreads();
-    if (!is_last || threadIdx.x >= 32) return;
-    __threadfence();
-    double s_kd = 0.0, s_ce = 0.0;
-    for (unsigned i = threadIdx.x; i < gridDim.x; i += 32) {
-        s_kd += __ldcg(A.part + i);
-        s_ce += __ldcg(A.part + A.slots + i);
-    }
-    s_kd = warp_sum(s_kd);
-    s_ce = warp_sum(s_ce);
-    if (threadIdx.x == 0) {
-        A.loss_out[0] = (float)(s_kd * A.l_kd);
-        A.loss_out[1] = (float)(s_ce * A.l_ce);
-        *A.ticket = 0u;  // ready for the next launch on this workspace
-    }
+// CTA partials -> workspace; the last CTA to arrive adds them in a fixed order, so the two
+// loss values are reproducible bit for bit (fixed grid => fixed summation tree).  Only warp 0
+// takes part after the one block barrier: lane 0 publishes with an acq_rel ticket (release of
+// its partial-sum stores, acquire of everybody else's), the verdict travels by shuffle, and the
+// other seven warps retire immediately instead of waiting for the ticket round trip.
+__device__ __forceinline__ unsigned ticket_acq_rel(unsigned *p) {
+    unsigned old;
+    asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(p) : "memory");
+    return old;
 }
 
 __device__ __forceinline__ void cta_reduce_and_publish(const LossArgs &A, double acc_kd, double acc_ce) {
@@ -200,15 +183,34 @@ __device__ __forceinline__ void cta_reduce_and_publish(const LossArgs &A, double
         sh[1][warp] = acc_ce;
     }
     __syncthreads();
-    double cta_kd = 0.0, cta_ce = 0.0;
-    if (threadIdx.x == 0) {
-        const int nw = blockDim.x >> 5;
-        for (int w = 0; w < nw; ++w) {
+    if (warp != 0) return;
+    unsigned t = 0;
+    if (lane == 0) {
+        double cta_kd = 0.0, cta_ce = 0.0;
+        for (int w = 0; w < kLossWarps; ++w) {
             cta_kd += sh[0][w];
             cta_ce += sh[1][w];
         }
+        A.part[blockIdx.x] = cta_kd;
+        A.part[A.slots + blockIdx.x] = cta_ce;
+        t = ticket_acq_rel(A.ticket);
     }
-    publish_loss(A, cta_kd, cta_ce);
+    t = __shfl_sync(0xffffffffu, t, 0);
+    if (t != gridDim.x - 1) return;
+    __threadfence();  // the other 31 lanes read the partials too: order their loads after the ticket
+    double s_kd = 0.0, s_ce = 0.0;
+#pragma unroll 4
+    for (unsigned i = lane; i < gridDim.x; i += 32) {
+        s_kd += __ldcg(A.part + i);
+        s_ce += __ldcg(A.part + A.slots + i);
+    }
+    s_kd = warp_sum(s_kd);
+    s_ce = warp_sum(s_ce);
+    if (lane == 0) {
+        A.loss_out[0] = (float)(s_kd * A.l_kd);
+        A.loss_out[1] = (float)(s_ce * A.l_ce);
+        *A.ticket = 0u;  // ready for the next launch on this scratch
+    }
 }
 
 #define MDB200_FOR4(V, BODY) \
@@ -219,7 +221,7 @@ __device__ __forceinline__ void cta_reduce_and_publish(const LossArgs &A, double
 // Requires classes % 4 == 0, 16-byte aligned rows, classes <= LPR*NV*4.
 // ---------------------------------------------------------------------------------------
 template <int LPR, int NV, bool DKD, int CE, bool SPLIT>
-__global__ void __launch_bounds__(kLossThreads) loss_rows_in_registers(const LossArgs A) {
+__global__ void __launch_bounds__(kLossThreads, (NV >= 16 ? 1 : 2)) loss_rows_in_registers(const LossArgs A) {
     constexpr int GPW = 32 / LPR;  // rows per warp
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int sub = lane % LPR, grp = lane / LPR;
@@ -452,11 +454,22 @@ __global__ void scale_by_scalar_kernel(float *out, const float *g, const float *
 // ---------------------------------------------------------------------------------------
 // host-side dispatch
 // ---------------------------------------------------------------------------------------
+// Resident CTAs per SM of a kernel at kLossThreads threads (register-limited); looked up once.
+template <typename Kernel>
+static int resident_ctas_per_sm(Kernel kernel) {
+    int n = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kLossThreads, 0) != cudaSuccess || n < 1) n = 1;
+    return n;
+}
+
+// Persistent grid: never more CTAs than the chip holds at once, so every CTA loops over an
+// (almost) equal share of the rows and there is no partial last wave.
 template <int LPR, int NV, bool DKD, int CE, bool SPLIT>
 static cudaError_t launch_regs(const LossArgs &A, int sms, cudaStream_t st) {
     constexpr int rows_per_cta = kLossWarps * (32 / LPR);
+    static const int occ = resident_ctas_per_sm(loss_rows_in_registers<LPR, NV, DKD, CE, SPLIT>);
     long long want = (A.rows + rows_per_cta - 1) / rows_per_cta;
-    const long long cap = (long long)sms * (NV >= 16 ? 2 : (NV >= 8 ? 4 : 8));
+    const long long cap = (long long)sms * occ;
     if (want > cap) want = cap;
     if (want > kMaxCtas) want = kMaxCtas;
     if (want > A.slots) return kGridExceedsSlots;
@@ -467,14 +480,16 @@ static cudaError_t launch_regs(const LossArgs &A, int sms, cudaStream_t st) {
 template <bool DKD, int CE, bool SPLIT>
 static cudaError_t launch_shape(const LossArgs &A, bool vec_ok, int sms, cudaStream_t st) {
     const long long nvec = A.classes >> 2;
+    if (vec_ok && nvec <= 28) return launch_regs<4, 7, DKD, CE, SPLIT>(A, sms, st);     // classes <= 112 (CIFAR-100: 25 of 28 slots)
     if (vec_ok && nvec <= 32) return launch_regs<8, 4, DKD, CE, SPLIT>(A, sms, st);
     if (vec_ok && nvec <= 128) return launch_regs<32, 4, DKD, CE, SPLIT>(A, sms, st);
-    if (vec_ok && nvec <= 256) return launch_regs<32, 8, DKD, CE, SPLIT>(A, sms, st);
+    if (vec_ok && nvec <= 256) return launch_regs<32, 8, DKD, CE, SPLIT>(A, sms, st);   // ImageNet-1k: 250 of 256 slots
     if constexpr (CE != 2) {  // a third 64-float register row would spill: general-T CE goes generic there
         if (vec_ok && nvec <= 512) return launch_regs<32, 16, DKD, CE, SPLIT>(A, sms, st);
     }
+    static const int occ = resident_ctas_per_sm(loss_rows_generic<DKD, CE, SPLIT>);
     long long want = A.rows;
-    const long long cap = (long long)sms * 8;
+    const long long cap = (long long)sms * occ;
     if (want > cap) want = cap;
     if (want > kMaxCtas) want = kMaxCtas;
     if (want > A.slots) return kGridExceedsSlots;

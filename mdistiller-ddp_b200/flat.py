@@ -23,7 +23,7 @@ def _round_up(x: int, m: int) -> int:
 
 
 class FlatSpace:
-    def __init__(self, params: Sequence[torch.Tensor], world_size: int = 1, rank: int = 0):
+    def __init__(self, params: Sequence[torch.Tensor], world_size: int = 1, rank: int = 0, flat_alloc=None):
         params = list(params)
         if not params:
             raise ValueError("no parameters")
@@ -48,7 +48,10 @@ class FlatSpace:
         self.shard_hi = self.shard_lo + self.shard_len
         # tensor i owns [offsets[i], ends[i]) including its alignment padding
         self.ends: List[int] = self.offsets[1:] + [self.total]
-        self.flat = torch.zeros(self.total, dtype=dt, device=dev)
+        # full-length buffers (P and the gradient buckets) may come from a special allocator
+        # (NVLink symmetric memory for the fused step); everything else is ordinary device memory
+        self._flat_alloc = flat_alloc
+        self.flat = self.new_flat_buffer()
         self._adopt()
 
     def _adopt(self) -> None:
@@ -57,6 +60,12 @@ class FlatSpace:
             for p, v in zip(self.params, self.views(self.flat)):
                 v.copy_(p.data)
                 p.data = v
+
+    def new_flat_buffer(self) -> torch.Tensor:
+        """Zeroed full-length buffer from the flat allocator (collective if that one is)."""
+        if self._flat_alloc is not None:
+            return self._flat_alloc(self.total, self.device)
+        return torch.zeros(self.total, dtype=torch.float32, device=self.device)
 
     def new_buffer(self) -> torch.Tensor:
         return torch.zeros(self.total, dtype=torch.float32, device=self.device)

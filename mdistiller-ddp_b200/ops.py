@@ -147,3 +147,38 @@ def sgd_step(p: torch.Tensor, g: torch.Tensor, v: Optional[torch.Tensor], *, lr:
                                  _stream_ptr(p.device))
     _lib.check(rc, "mdb200_sgd_step")
     launch_count += 1
+
+
+def dot_step_fused(p_local: torch.Tensor, g_task_local: torch.Tensor, g_kd_local: torch.Tensor,
+                   v_task: Optional[torch.Tensor], v_kd: torch.Tensor, *, multicast=None, peers=None,
+                   kd_is_reduced: bool, shard_lo: int, shard_len: int, world: int, lr: float, momentum: float,
+                   momentum_kd: float, weight_decay: float = 0.0, dampening: float = 0.0, grad_scale: float = 1.0,
+                   first_task: bool = False, first_kd: bool = False) -> None:
+    """Fused reduce + DOT update + broadcast for this rank's shard (see mdb200_dot_step_fused).
+
+    ``multicast`` = (p_mc, g_task_mc, g_kd_mc) integer multicast addresses or None;
+    ``peers`` = (p_ptrs, g_task_ptrs, g_kd_ptrs), each a list of ``world`` integer base addresses.
+    """
+    global launch_count
+    import ctypes as C
+    lib = _lib.load()
+    n = p_local.numel()
+    ptrs = (_flat_ptr(p_local, "p_local", n), _flat_ptr(g_task_local, "g_task_local", n),
+            _flat_ptr(g_kd_local, "g_kd_local", n), _flat_ptr(v_task, "v_task", shard_len),
+            _flat_ptr(v_kd, "v_kd", shard_len))
+    mc = multicast if multicast is not None else (None, None, None)
+
+    def table(addrs):
+        if addrs is None:
+            return None
+        return (C.c_void_p * world)(*[int(a) for a in addrs])
+
+    pt = peers if peers is not None else (None, None, None)
+    tabs = [table(t) for t in pt]
+    with torch.cuda.device(p_local.device):
+        rc = lib.mdb200_dot_step_fused(
+            ptrs[0], mc[0] or None, tabs[0], ptrs[1], mc[1] or None, tabs[1], ptrs[2], mc[2] or None, tabs[2],
+            int(kd_is_reduced), ptrs[3], ptrs[4], shard_lo, shard_len, world, lr, momentum, momentum_kd,
+            weight_decay, dampening, grad_scale, int(first_task), int(first_kd), _stream_ptr(p_local.device))
+    _lib.check(rc, "mdb200_dot_step_fused")
+    launch_count += 1

@@ -44,12 +44,13 @@ class _FlatOptimizer(Optimizer):
         self._k = kernels if kernels is not None else ops
         self._comm = comm if comm is not None else ShardComm()
         plist = self.param_groups[0]["params"]
-        self._space = FlatSpace(plist, self._comm.world_size, self._comm.rank)
+        self._space = FlatSpace(plist, self._comm.world_size, self._comm.rank,
+                                flat_alloc=getattr(self._comm, "alloc_flat", None))
         self._comm.broadcast(self._space.flat, src=0)       # DDP's constructor does the same
         self._buckets: Dict[str, torch.Tensor] = {}
         self._views: Dict[str, List[torch.Tensor]] = {}
         for name in self._bucket_names:
-            b = self._space.new_buffer()
+            b = self._space.new_flat_buffer()
             self._buckets[name] = b
             self._views[name] = self._space.views(b)
         self._phase = self._bucket_names[0]
@@ -187,6 +188,8 @@ class DistillationOrientedTrainer(_FlatOptimizer):
         self._has_vk = [False] * n     # 'momentum_kd_buffer' exists (dot.py:168-170)
         self._kd_members: Optional[List[bool]] = None
         self._kd_work = None
+        self._kd_prereduced = True
+        self.last_fused = None          # set by every fused step: {"multicast": bool, "kd_in_kernel": bool}
 
     @torch.no_grad()
     def step_kd(self, closure=None):
@@ -197,7 +200,10 @@ class DistillationOrientedTrainer(_FlatOptimizer):
         assert len(self.param_groups) == 1, "Only implement for one-group params."
         self._kd_members = self._collect("kd")
         # the KD bucket is complete: start its reduce-scatter now so it overlaps backward #2
-        self._kd_work = self._comm.reduce_scatter_sum(self._buckets["kd"], async_op=True)
+        # (unless the fused step kernel is going to pull it through the switch itself)
+        self._kd_prereduced = not (getattr(self._comm, "fused", False) and self._comm.fuse_kd)
+        if self._kd_prereduced:
+            self._kd_work = self._comm.reduce_scatter_sum(self._buckets["kd"], async_op=True)
         self._phase = "task"
         return loss
 
@@ -211,31 +217,39 @@ class DistillationOrientedTrainer(_FlatOptimizer):
         group = self.param_groups[0]
         task_members = self._collect("task")
         kd_members = self._kd_members if self._kd_members is not None else [False] * len(task_members)
-        work = self._comm.reduce_scatter_sum(self._buckets["task"], async_op=True)
-        for w in (self._kd_work, work):
-            if w is not None:
-                w.wait()
-        self._kd_work = None
-
         modes = []
         for i, (t, k) in enumerate(zip(task_members, kd_members)):
             m = (_BOTH if k else _TASK) if t else (_KD if k else _NONE)
             modes.append((m, t and not self._has_vt[i], k and not self._has_vk[i]))
         sp = self._space
         momentum = group["momentum"]
-        for lo, hi, (m, first_t, first_k) in self._runs(modes):
-            a, b = lo - sp.shard_lo, hi - sp.shard_lo
-            self._k.dot_step(
-                sp.flat[lo:hi],
-                self._buckets["task"][lo:hi] if m != _KD else None,
-                self._buckets["kd"][lo:hi] if m != _TASK else None,
-                self._v_task[a:b] if (m != _KD and momentum != 0) else None,
-                self._v_kd[a:b] if m != _TASK else None,
-                lr=group["lr"], momentum=momentum, momentum_kd=group["momentum_kd"],
-                weight_decay=group["weight_decay"], dampening=group["dampening"],
-                grad_scale=1.0 / self._comm.world_size, first_task=first_t, first_kd=first_k,
-                membership=_MEMBERSHIP[m])
-        self._comm.all_gather(sp.flat)
+        runs = self._runs(modes)
+        hp = dict(lr=group["lr"], momentum=momentum, momentum_kd=group["momentum_kd"],
+                  weight_decay=group["weight_decay"], dampening=group["dampening"],
+                  grad_scale=1.0 / self._comm.world_size)
+        fused = (getattr(self._comm, "fused", False) and self._comm.world_size > 1 and len(runs) == 1
+                 and runs[0][0] == sp.shard_lo and runs[0][1] == sp.shard_hi and runs[0][2][0] == _BOTH
+                 and self._kd_members is not None)
+        if fused:
+            self._fused_step(runs[0][2], hp)
+        else:
+            if getattr(self, "_kd_prereduced", True) is False:   # KD bucket was left for a fused step that cannot run
+                self._kd_work = self._comm.reduce_scatter_sum(self._buckets["kd"], async_op=True)
+            work = self._comm.reduce_scatter_sum(self._buckets["task"], async_op=True)
+            for w in (self._kd_work, work):
+                if w is not None:
+                    w.wait()
+            self._kd_work = None
+            for lo, hi, (m, first_t, first_k) in runs:
+                a, b = lo - sp.shard_lo, hi - sp.shard_lo
+                self._k.dot_step(
+                    sp.flat[lo:hi],
+                    self._buckets["task"][lo:hi] if m != _KD else None,
+                    self._buckets["kd"][lo:hi] if m != _TASK else None,
+                    self._v_task[a:b] if (m != _KD and momentum != 0) else None,
+                    self._v_kd[a:b] if m != _TASK else None,
+                    first_task=first_t, first_kd=first_k, membership=_MEMBERSHIP[m], **hp)
+            self._comm.all_gather(sp.flat)
 
         for i, (t, k) in enumerate(zip(task_members, kd_members)):
             if t and momentum != 0:
@@ -245,6 +259,26 @@ class DistillationOrientedTrainer(_FlatOptimizer):
         self._kd_members = None
         self._phase = "kd"
         return loss
+
+    def _fused_step(self, mode, hp) -> None:
+        """gradient sum over ranks -> update -> parameters to every rank, one launch (dot_fused.cu)."""
+        comm, sp = self._comm, self._space
+        _, first_t, first_k = mode
+        if self._kd_work is not None:
+            self._kd_work.wait()
+            self._kd_work = None
+        p, gt, gk = sp.flat, self._buckets["task"], self._buckets["kd"]
+        (p_mc, p_peers), (gt_mc, gt_peers), (gk_mc, gk_peers) = (comm.addresses(t) for t in (p, gt, gk))
+        use_mc = bool(p_mc and gt_mc and gk_mc)
+        self.last_fused = {"multicast": use_mc, "kd_in_kernel": not self._kd_prereduced}
+        comm.barrier(p, channel=0)          # every rank's second backward (and KD reduce-scatter) has landed
+        self._k.dot_step_fused(
+            p, gt, gk, self._v_task if hp["momentum"] != 0 else None, self._v_kd,
+            multicast=(p_mc, gt_mc, gk_mc) if use_mc else None,
+            peers=None if use_mc else (p_peers, gt_peers, gk_peers),
+            kd_is_reduced=self._kd_prereduced, shard_lo=sp.shard_lo, shard_len=sp.shard_len,
+            world=comm.world_size, first_task=first_t, first_kd=first_k, **hp)
+        comm.barrier(p, channel=1)          # nobody reads P before every shard owner has written it
 
     # -- reference checkpoint layout: state[p]['momentum_buffer'|'momentum_kd_buffer'] -----
     def state_dict(self):

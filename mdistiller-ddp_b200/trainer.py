@@ -15,13 +15,14 @@ Differences from the reference, all documented reference defects
 
 from __future__ import annotations
 
+import os
 import time
 from typing import Dict, Optional
 
 import torch
 import torch.distributed as dist
 
-from .comm import ShardComm
+from .comm import ShardComm, SymmetricShardComm
 from .optim import DistillationOrientedTrainer, FlatSGD
 
 
@@ -56,12 +57,22 @@ class TailStepMixin:
     ``self.distiller``, ``self.cfg`` and (after init) ``self.optimizer``."""
 
     trainer_kind = "dot"   # "dot" | "base"
+    # how the data-parallel DOT step talks: "nccl" = reduce-scatter / update / all-gather launches,
+    # "fused" = one kernel over NVLink symmetric memory (KD bucket still on an overlapped NCCL
+    # reduce-scatter), "fused_kd" = both buckets in the kernel, "*_p2p" = no NVSwitch multicast
+    comm_mode = os.environ.get("MDB200_COMM", "nccl")
 
     # ---------------------------------------------------------------- optimizer
     def init_optimizer(self, cfg):
         core = _unwrap(self.distiller)
         silence_ddp_reducer(self.distiller)
-        comm = ShardComm() if (dist.is_available() and dist.is_initialized()) else None
+        comm = None
+        if dist.is_available() and dist.is_initialized():
+            mode = self.comm_mode
+            if mode != "nccl" and self.trainer_kind == "dot" and dist.get_world_size() > 1:
+                comm = SymmetricShardComm(fuse_kd=mode.startswith("fused_kd"), use_multicast=not mode.endswith("p2p"))
+            else:
+                comm = ShardComm()
         params = core.get_learnable_parameters()
         if self.trainer_kind == "dot":
             if cfg.EXPERIMENT.AMP:

@@ -21,7 +21,15 @@ def _need_gpus(n):
         pytest.skip(f"needs {n} GPUs, have {torch.cuda.device_count()}")
 
 
-def _opt_worker(rank, world, port, case_idx, out):
+def _make_comm(mode):
+    from mdistiller_ddp_b200.comm import ShardComm, SymmetricShardComm
+    if mode == "nccl":
+        return ShardComm()
+    return SymmetricShardComm(fuse_kd=(mode in ("fused_kd", "fused_kd_p2p")),
+                              use_multicast=not mode.endswith("p2p"), barrier_timeout_ms=15000)
+
+
+def _opt_worker(rank, world, port, case_idx, out, mode="nccl"):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
@@ -30,7 +38,8 @@ def _opt_worker(rank, world, port, case_idx, out):
         case = _cases.DOT_CASES[case_idx]
         params = [torch.nn.Parameter((p.clone() + (0.5 if rank else 0.0)).cuda()) for p in _cases.make_params(case)]
         opt = b200.DistillationOrientedTrainer(params, lr=case.lr, momentum=case.momentum - case.delta,
-                                               momentum_kd=case.momentum + case.delta, weight_decay=case.wd)
+                                               momentum_kd=case.momentum + case.delta, weight_decay=case.wd,
+                                               comm=_make_comm(mode))
         assert opt.world_size == world
         shapes = [p.shape for p in params]
         # per-rank gradient factors with mean 1 over ranks
@@ -60,12 +69,17 @@ def _opt_worker(rank, world, port, case_idx, out):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,case_idx", [(2, 0), (2, 2), (4, 6), (8, 6)])
-def test_sharded_dot_step_matches_oracle_on_rank_averaged_gradients(world, case_idx, tmp_path):
+@pytest.mark.parametrize("world,case_idx,mode", [
+    (2, 0, "nccl"), (2, 2, "nccl"), (4, 6, "nccl"), (8, 6, "nccl"),
+    # one fused kernel over NVLink symmetric memory: NVLS multicast, both buckets in-switch, plain peer access
+    (2, 0, "fused"), (2, 6, "fused_kd"), (2, 6, "fused_p2p"), (2, 2, "fused"),
+    (8, 6, "fused"), (8, 6, "fused_kd"), (8, 6, "fused_kd_p2p"),
+])
+def test_sharded_dot_step_matches_oracle_on_rank_averaged_gradients(world, case_idx, mode, tmp_path):
     _need_gpus(world)
     out = str(tmp_path / "r0.pt")
-    port = 29600 + (os.getpid() % 1500) + world * 3 + case_idx
-    mp.spawn(_opt_worker, args=(world, port, case_idx, out), nprocs=world, join=True)
+    port = 29600 + (os.getpid() % 1500) + world * 3 + case_idx + 17 * len(mode)
+    mp.spawn(_opt_worker, args=(world, port, case_idx, out, mode), nprocs=world, join=True)
     got = torch.load(out, weights_only=False)
     case = _cases.DOT_CASES[case_idx]
     params = [p.clone() for p in _cases.make_params(case)]

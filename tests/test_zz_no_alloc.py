@@ -68,8 +68,10 @@ def test_static_scratch_entry_point_refuses_launches_beyond_its_slots():
     sms = torch.cuda.get_device_properties(0).multi_processor_count
     if sms * 8 <= 1024:
         pytest.skip("this GPU never needs more than 1024 thread blocks")
-    zs, zt, y = _inputs(40000, 100, 3)          # 1250 blocks wanted, capped at 8 per SM > 1024 slots
-    rc, loss, gk, gc = _call_static(lib, zs, zt, y, ops.LOSS_DKD, 1.0, 8.0, 4.0, ops.CE_NONE)
+    # 101 classes is off the vector path: one row per block, 8 resident blocks per SM in KD mode,
+    # so 2000 rows want min(2000, 8 * SMs) > 1024 blocks
+    zs, zt, y = _inputs(2000, 101, 3)
+    rc, loss, gk, gc = _call_static(lib, zs, zt, y, ops.LOSS_KD, 1.0, 1.0, 4.0, ops.CE_NONE)
     assert rc == ESCRATCH
     assert b"built-in scratch" in lib.mdb200_error_string(rc)
     # the refusal launched nothing and left the scratch usable
