@@ -47,8 +47,11 @@ def parse():
     ap.add_argument("--workload", default="imagenet_r34_r18_dkd_dot")
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (0 = the workload's)")
     ap.add_argument("--cpu-batch", type=int, default=16, help="bounded CPU sample: images per CPU step")
-    ap.add_argument("--comm", default="nccl", choices=["nccl", "fused", "fused_kd", "fused_p2p", "fused_kd_p2p"],
-                    help="data-parallel step: NCCL launches or the fused NVLink kernel (N > 1)")
+    ap.add_argument("--comm", default="auto",
+                    choices=["auto", "nccl", "fused", "fused_kd", "fused_p2p", "fused_kd_p2p"],
+                    help="data-parallel step (N > 1): NCCL launches or the fused NVLink kernel; auto = fused "
+                         "(peer access at N <= 2, NVSwitch multicast with both buckets in the kernel above), "
+                         "NCCL launches if symmetric memory cannot be set up")
     ap.add_argument("--no-sweep", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     return ap.parse_args()
@@ -259,8 +262,21 @@ def run_b200_arm(args):
     teacher, student, hw, classes = W.build_pair(args.workload, seed=0)
     cfg = W.default_cfg(args.workload)
     distiller = b200.distiller_dict[cfg.DISTILLER.TYPE](student, teacher, cfg).to(dev).train()
-    b200.TailStepMixin.comm_mode = args.comm
-    trainer = b200.StandaloneTrainer(distiller, cfg)
+    comm_mode = args.comm
+    if comm_mode == "auto":
+        comm_mode = "nccl" if world == 1 else ("fused_p2p" if world <= 2 else "fused_kd")
+    comm_note = ""
+    b200.TailStepMixin.comm_mode = comm_mode
+    try:
+        trainer = b200.StandaloneTrainer(distiller, cfg)
+    except Exception as e:                      # symmetric memory / multicast not available on this box
+        if comm_mode == "nccl" or args.comm != "auto":
+            raise
+        comm_note = f" (fused step unavailable: {type(e).__name__}: {str(e)[:120]}; using NCCL launches)"
+        comm_mode = "nccl"
+        b200.TailStepMixin.comm_mode = comm_mode
+        trainer = b200.StandaloneTrainer(distiller, cfg)
+    args.comm = comm_mode
     n_params = sum(p.numel() for p in distiller.get_learnable_parameters())
     shard_elems = trainer.optimizer._space.shard_len
 
@@ -351,12 +367,35 @@ def run_b200_arm(args):
     step_t = [a.elapsed_time(b) * 1e-3 for a, b in probes["opt_step"]]
     loss_bytes = 16 * per_gpu * classes + 8 * per_gpu + 8
 
+    fused_info = getattr(trainer.optimizer, "last_fused", None)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
     h2d = sum(t.numel() * t.element_size() for t in host[:2])
+    if fused_info is None:
+        roofline = {"kernel": "flat_step_vec4<true,true> (mdb200_dot_step)", "bound": "hbm",
+                    "achieved": dot_bytes / dot_avg / 1e9, "peak": peak, "unit": "GB/s",
+                    "frac": dot_bytes / dot_avg / 1e9 / peak, "traffic": profiled_traffic("dot_step", shard_elems),
+                    "peak_source": peak_src, "bytes_per_launch": dot_bytes, "us_per_launch": dot_avg * 1e6,
+                    "launches_timed": len(dot_t),
+                    "note": "timed in-step right after backward: part of the 234 MB working set is L2-resident"}
+    else:
+        # fused reduce + update + broadcast kernel: the bytes that must cross NVLink bound it, not HBM
+        S, W = 4 * shard_elems, world
+        nb = 2 if fused_info["kd_in_kernel"] else 1
+        if fused_info["multicast"]:     # every replica of a bucket shard travels to the switch once; P comes back W times
+            out_b, in_b = nb * W * S + S, nb * S + W * S
+        else:
+            out_b, in_b = nb * (W - 1) * S + (W - 1) * S, nb * (W - 1) * S + (W - 1) * S
+        link = max(out_b, in_b)
+        roofline = {"kernel": "dot_fused_shard (mdb200_dot_step_fused)", "bound": "nvlink",
+                    "achieved": link / dot_avg / 1e9, "peak": 770.0, "unit": "GB/s", "frac": link / dot_avg / 1e9 / 770.0,
+                    "traffic": None, "peak_source": "B200_PROFILING.md: measured peer copy 770 GB/s per direction per GPU",
+                    "bytes_per_launch": link, "us_per_launch": dot_avg * 1e6, "launches_timed": len(dot_t),
+                    "note": f"bytes = busier NVLink direction per GPU (out {out_b}, in {in_b}); HBM-side algorithmic "
+                            f"bytes are {dot_bytes}; mode {fused_info}"}
     line = {
         "metric": METRIC, "value": world * per_gpu * args.steps / secs, "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * secs / args.steps,
@@ -365,7 +404,7 @@ def run_b200_arm(args):
                                f"1000 classes, random-init" if args.workload == "imagenet_r34_r18_dkd_dot" else args.workload,
                    "per_gpu_batch": per_gpu, "global_batch": per_gpu * world, "student_params": n_params,
                    "parallelism": (f"dp{world}: reduce-scatter x2 -> DOT on 1/{world} shard -> all-gather (NCCL)" if args.comm == "nccl" or world == 1
-                                   else f"dp{world}: fused NVLink kernel ({args.comm}): in-switch gradient sum -> DOT on 1/{world} shard -> multicast store"),
+                                   else f"dp{world}: fused NVLink kernel ({args.comm}): gradient sum over ranks -> DOT on 1/{world} shard -> parameters to every rank") + comm_note,
                    "backbone_math": "fp32 storage, cuDNN TF32 convolutions allowed (torch default, as the reference)",
                    "l2": "inputs_exceed_l2 (154 MB batch, >1 GB activations per step)"},
         "e2e": {"value": world * per_gpu * args.steps / e2e_secs, "unit": UNIT, "h2d_bytes_per_step": h2d,
@@ -378,12 +417,7 @@ def run_b200_arm(args):
                                    "CUDA events on the compute stream", "comm": args.comm if world > 1 else "none",
                            "fused": getattr(trainer.optimizer, "last_fused", None)},
         "clocks": clocks,
-        "roofline": {"kernel": "flat_step_vec4<true,true> (mdb200_dot_step)", "bound": "hbm",
-                     "achieved": dot_bytes / dot_avg / 1e9, "peak": peak, "unit": "GB/s",
-                     "frac": dot_bytes / dot_avg / 1e9 / peak, "traffic": profiled_traffic("dot_step", shard_elems),
-                     "peak_source": peak_src, "bytes_per_launch": dot_bytes, "us_per_launch": dot_avg * 1e6,
-                     "launches_timed": len(dot_t),
-                     "note": "timed in-step right after backward: part of the 234 MB working set is L2-resident"},
+        "roofline": roofline,
         "loss_kernel_in_step": {"kernel": "loss_rows_in_registers (mdb200_distill_loss)", "us_per_launch": loss_avg * 1e6,
                                 "bytes_per_launch": loss_bytes, "GB/s": loss_bytes / loss_avg / 1e9,
                                 "note": "256x1000 is 4 MB: launch-latency bound, see kernels{} for the large-shape sweep"},

@@ -27,7 +27,7 @@ namespace mdb200 {
 
 constexpr int kMaxPeers = 16;
 constexpr int kFusedThreads = 256;
-constexpr int kFusedUnroll = 2;
+constexpr int kFusedUnroll = 4;   // 4 remote 16-byte requests per gradient bucket in flight per thread
 
 struct FusedCoef {
     float neg_lr, m_task, m_kd, wd, keep, gscale;
@@ -94,9 +94,15 @@ dot_fused_shard(float4 *p_local, float4 *p_mc, const PeerTable p_peers,
 #pragma unroll
         for (int u = 0; u < kFusedUnroll; ++u) {
             const long long i = t0 + u * kFusedThreads + threadIdx.x;
-            if (i < n4) {
+            if (i < n4) {   // NVLink requests first: they have the longest way to go
                 GT[u] = fetch_grad<SRC_T>(gt_src, gt_peers, world, i);
                 GK[u] = fetch_grad<SRC_K>(gk_src, gk_peers, world, i);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kFusedUnroll; ++u) {
+            const long long i = t0 + u * kFusedThreads + threadIdx.x;
+            if (i < n4) {
                 P[u] = ld_stream_rw(p_local + i);
                 if (use_vt && !c.first_task) VT[u] = ld_stream_rw(vt + i);
                 if (!c.first_kd) VK[u] = ld_stream_rw(vk + i);
