@@ -15,13 +15,13 @@ from .optim import DistillationOrientedTrainer, FlatSGD  # noqa: F401
 from .comm import ShardComm  # noqa: F401
 from .flat import FlatSpace  # noqa: F401
 from .trainer import TailStepMixin, StandaloneTrainer, new_train_meters, silence_ddp_reducer  # noqa: F401
-from .install import install  # noqa: F401
+from .install import install, uninstall  # noqa: F401
 
 distiller_dict = {"DKD": DKD, "KD": KD}
 
 __all__ = [
     "dkd_loss", "kd_loss", "distill_tail", "TailResult", "Distiller", "DKD", "KD",
     "DistillationOrientedTrainer", "FlatSGD", "ShardComm", "FlatSpace", "TailStepMixin",
-    "StandaloneTrainer", "new_train_meters", "silence_ddp_reducer", "install", "distiller_dict",
+    "StandaloneTrainer", "new_train_meters", "silence_ddp_reducer", "install", "uninstall", "distiller_dict",
     "build_library", "LIB_PATH", "ops",
 ]

@@ -17,6 +17,8 @@ from __future__ import annotations
 import importlib
 import sys
 
+_saved = {}
+
 
 def install(replace_base: bool = True):
     """Returns the dict of patched objects; raises ImportError if `mdistiller` is not importable."""
@@ -28,6 +30,13 @@ def install(replace_base: bool = True):
     ref_trainer = importlib.import_module("mdistiller.engine.trainer")
     ref_dot = importlib.import_module("mdistiller.engine.dot")
 
+    if not _saved:
+        _saved.update(
+            DKD=ref_distillers.distiller_dict["DKD"], KD=ref_distillers.distiller_dict["KD"],
+            dkd_loss=sys.modules["mdistiller.distillers.DKD"].dkd_loss,
+            kd_loss=sys.modules["mdistiller.distillers.KD"].kd_loss,
+            opt_dot=ref_dot.DistillationOrientedTrainer, opt_trainer=ref_trainer.DistillationOrientedTrainer,
+            dot=ref_engine.trainer_dict["dot"], base=ref_engine.trainer_dict["base"])
     ref_distillers.distiller_dict["DKD"] = distillers.DKD
     ref_distillers.distiller_dict["KD"] = distillers.KD
     # `mdistiller.distillers.DKD` is the class (the package __init__ shadows the module name),
@@ -57,3 +66,20 @@ def install(replace_base: bool = True):
         ref_engine.trainer_dict["base"] = Base
         patched["base"] = Base
     return patched
+
+
+def uninstall() -> None:
+    """Put the reference's own objects back (used by tests that share a process with the oracle)."""
+    if not _saved:
+        return
+    ref_distillers = importlib.import_module("mdistiller.distillers")
+    ref_engine = importlib.import_module("mdistiller.engine")
+    ref_trainer = importlib.import_module("mdistiller.engine.trainer")
+    ref_dot = importlib.import_module("mdistiller.engine.dot")
+    ref_distillers.distiller_dict["DKD"], ref_distillers.distiller_dict["KD"] = _saved["DKD"], _saved["KD"]
+    sys.modules["mdistiller.distillers.DKD"].dkd_loss = _saved["dkd_loss"]
+    sys.modules["mdistiller.distillers.KD"].kd_loss = _saved["kd_loss"]
+    ref_dot.DistillationOrientedTrainer = _saved["opt_dot"]
+    ref_trainer.DistillationOrientedTrainer = _saved["opt_trainer"]
+    ref_engine.trainer_dict["dot"], ref_engine.trainer_dict["base"] = _saved["dot"], _saved["base"]
+    _saved.clear()

@@ -30,7 +30,7 @@ def lib():
 def test_header_declares_the_expected_surface():
     assert set(_declared()) >= {"mdb200_abi_version", "mdb200_error_string", "mdb200_loss_workspace_bytes",
                                 "mdb200_distill_loss", "mdb200_scale_by_device_scalar", "mdb200_dot_step",
-                                "mdb200_sgd_step"}
+                                "mdb200_sgd_step", "mdb200_dot_step_fused", "mdb200_distill_loss_static_scratch"}
 
 
 def test_every_declared_symbol_is_exported_and_bound(lib):
@@ -64,6 +64,15 @@ def test_argument_errors_are_reported_before_any_cuda_work(lib):
     assert lib.mdb200_dot_step(p, p, p, p, p, 16, .1, .9, .9, 0., 0., 1., 0, 0, 9, None) == -1
     assert lib.mdb200_dot_step(p, p, p, p, p, 0, .1, .9, .9, 0., 0., 1., 0, 0, 0, None) == 0   # empty range
     assert lib.mdb200_sgd_step(p, p, None, 16, .1, .9, 0., 0., 1., 0, None) == -1            # momentum needs v
+    fused = lambda **kw: lib.mdb200_dot_step_fused(  # noqa: E731
+        kw.get("p", p), None, None, p, None, None, p, None, None, 1, p, p, kw.get("lo", 0), kw.get("n", 16),
+        kw.get("world", 2), .1, .9, .9, 0., 0., .5, 0, 0, None)
+    assert fused() == -1                       # neither multicast addresses nor peer tables
+    assert fused(world=17) == -1               # more peers than the kernel addresses
+    assert fused(lo=2) == -4                   # shard must start on a 16-byte slot
+    assert fused(p=None) == -1
+    assert lib.mdb200_distill_loss_static_scratch(None, None, None, 4, 8, 8, 8, 0, 1., 1., 1., 1., 0, 1.,
+                                                  None, None, 8, None, None) == -1
 
 
 def test_ops_refuse_cpu_tensors():

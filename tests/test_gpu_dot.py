@@ -163,3 +163,100 @@ def test_trainer_step_matches_cpu_oracle_end_to_end(b200):
         assert abs(losses["loss_ce"].item() - l_ce.item()) <= 1e-4 * abs(l_ce.item())
     for (name, p), q in zip(student.named_parameters(), cpu_params):
         assert oracle.max_rel_err(p, q) <= 1e-4, name     # cuDNN vs CPU conv rounding dominates here
+
+
+@pytest.mark.parametrize("kind", ["DKD", "KD"])
+def test_base_trainer_step_matches_cpu_oracle(kind, b200):
+    """Non-DOT configs (BaseTrainer.train_iter, trainer.py:257-321): summed loss, one backward,
+    torch.optim.SGD -- here: combined-gradient tail + FlatSGD."""
+    from mdistiller_ddp_b200 import workloads as W
+    import copy
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(1)
+    teacher, student = W.TinyNet(100, 24), W.TinyNet(100, 16)
+    cpu_t, cpu_s = copy.deepcopy(teacher).eval(), copy.deepcopy(student).train()
+    cfg = W.default_cfg("cifar_res32x4_res8x4_dkd_base")
+    cfg.DISTILLER.TYPE = kind
+    dist_gpu = b200.distiller_dict[kind](student, teacher, cfg).cuda().train()
+    tr = b200.StandaloneTrainer(dist_gpu, cfg, kind="base")
+    assert dist_gpu.combined_tail
+    ref_opt = torch.optim.SGD(cpu_s.parameters(), lr=cfg.SOLVER.LR, momentum=cfg.SOLVER.SGD.MOMENTUM,
+                              weight_decay=cfg.SOLVER.WEIGHT_DECAY)
+    for step in range(4):
+        image, target, _ = W.synthetic_batch(32, 32, 100, seed=10 + step)
+        epoch = 7
+        preds, losses = tr.tail_step(image.cuda(), target.cuda(), epoch)
+        ref_opt.zero_grad()
+        zs, _ = cpu_s(image)
+        with torch.no_grad():
+            zt, _ = cpu_t(image)
+        if kind == "DKD":
+            l_ce = cfg.DKD.CE_WEIGHT * oracle.ce_loss(zs, target)
+            l_kd = min(epoch / cfg.DKD.WARMUP, 1.0) * oracle.dkd_loss(zs, zt, target, cfg.DKD.ALPHA, cfg.DKD.BETA, cfg.DKD.T)
+        else:
+            l_ce = cfg.KD.LOSS.CE_WEIGHT * oracle.ce_loss(zs, target)
+            l_kd = cfg.KD.LOSS.KD_WEIGHT * oracle.kd_loss(zs, zt, cfg.KD.TEMPERATURE)
+        (l_ce + l_kd).backward()
+        ref_opt.step()
+        assert abs(losses["loss_kd"].item() - l_kd.item()) <= 1e-4 * abs(l_kd.item())
+        assert abs(losses["loss_ce"].item() - l_ce.item()) <= 1e-4 * abs(l_ce.item())
+    for (name, p), q in zip(student.named_parameters(), cpu_s.parameters()):
+        assert oracle.max_rel_err(p, q) <= 1e-4, name
+
+
+def test_kd_dot_trainer_step_matches_cpu_oracle(b200):
+    """configs[1]: KD + DOT (KD.forward_train, KD.py:25-39, T = 4, CE 0.1 / KD 0.9)."""
+    from mdistiller_ddp_b200 import workloads as W
+    import copy
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(2)
+    teacher, student = W.TinyNet(100, 24), W.TinyNet(100, 16)
+    cpu_t, cpu_s = copy.deepcopy(teacher).eval(), copy.deepcopy(student).train()
+    cfg = W.default_cfg("cifar_res32x4_res8x4_kd_dot")
+    tr = b200.StandaloneTrainer(b200.KD(student, teacher, cfg).cuda().train(), cfg, kind="dot")
+    cpu_params = [p for _, p in cpu_s.named_parameters()]
+    m, d = cfg.SOLVER.SGD.MOMENTUM, cfg.SOLVER.DOT.DELTA
+    ref = oracle.DotListOracle([p.data for p in cpu_params], lr=cfg.SOLVER.LR, momentum=m - d, momentum_kd=m + d,
+                               weight_decay=cfg.SOLVER.WEIGHT_DECAY)
+    for step in range(4):
+        image, target, _ = W.synthetic_batch(32, 32, 100, seed=20 + step)
+        tr.tail_step(image.cuda(), target.cuda(), 1)
+        zs, _ = cpu_s(image)
+        with torch.no_grad():
+            zt, _ = cpu_t(image)
+        l_ce = cfg.KD.LOSS.CE_WEIGHT * oracle.ce_loss(zs, target)
+        l_kd = cfg.KD.LOSS.KD_WEIGHT * oracle.kd_loss(zs, zt, cfg.KD.TEMPERATURE)
+        g_kd = torch.autograd.grad(l_kd, cpu_params, retain_graph=True)
+        g_ce = torch.autograd.grad(l_ce, cpu_params)
+        ref.step_kd(list(g_kd))
+        ref.step(list(g_ce))
+    for (name, p), q in zip(student.named_parameters(), cpu_params):
+        assert oracle.max_rel_err(p, q) <= 1e-4, name
+
+
+def test_generic_autograd_protocol_equals_seeded_backward(b200):
+    """The reference call pattern (loss_kd.backward(retain_graph=True); step_kd(); loss_ce.backward();
+    step()) through autograd gives the same parameters as the trainer's seeded-backward shortcut."""
+    from mdistiller_ddp_b200 import workloads as W
+    import copy
+    torch.manual_seed(3)
+    teacher, student = W.TinyNet(100, 24), W.TinyNet(100, 16)
+    t2, s2 = copy.deepcopy(teacher), copy.deepcopy(student)
+    cfg = W.default_cfg("cifar_res32x4_res8x4_kd_dot")
+    fast = b200.StandaloneTrainer(b200.DKD(student, teacher, cfg).cuda().train(), cfg, kind="dot")
+    slow_d = b200.DKD(s2, t2, cfg).cuda().train()
+    slow = b200.StandaloneTrainer(slow_d, cfg, kind="dot")
+    for step in range(3):
+        image, target, _ = W.synthetic_batch(16, 32, 100, seed=30 + step)
+        image, target = image.cuda(), target.cuda()
+        fast.tail_step(image, target, 4)
+        opt = slow.optimizer
+        preds, losses = slow_d(image=image, target=target, epoch=4)
+        opt.zero_grad(set_to_none=True)
+        losses["loss_kd"].backward(retain_graph=True)
+        opt.step_kd()
+        opt.zero_grad(set_to_none=True)
+        losses["loss_ce"].backward()
+        opt.step()
+    for p, q in zip(student.parameters(), s2.parameters()):
+        assert oracle.max_rel_err(p, q) <= 1e-6      # identical arithmetic; cuDNN backward is not bitwise repeatable
