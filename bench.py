@@ -305,6 +305,7 @@ def run_b200_arm(args):
     opt = trainer.optimizer
     opt.step = wrap("opt_step", opt.step)
     ops.dot_step = wrap("dot", orig_dot)
+    ops.sgd_step = wrap("dot", ops.sgd_step)
     ops.dot_step_fused = wrap("dot", orig_fused)
     ops.distill_loss = wrap("loss", orig_loss)
     # losses.py / optim.py call through the `ops` module attribute, so the wrappers are seen
@@ -362,10 +363,11 @@ def run_b200_arm(args):
     loss_t = [a.elapsed_time(b) * 1e-3 for a, b in probes["loss"]]
     peak, peak_src = hbm_peak()
     dot_avg = sum(dot_t) / len(dot_t)
-    dot_bytes = 32 * shard_elems
+    is_dot = cfg.SOLVER.TRAINER == "dot"
+    dot_bytes = (32 if is_dot else 20) * shard_elems
     loss_avg = sum(loss_t) / len(loss_t)
     step_t = [a.elapsed_time(b) * 1e-3 for a, b in probes["opt_step"]]
-    loss_bytes = 16 * per_gpu * classes + 8 * per_gpu + 8
+    loss_bytes = (16 if is_dot else 12) * per_gpu * classes + 8 * per_gpu + 8
 
     fused_info = getattr(trainer.optimizer, "last_fused", None)
     if rank != 0:
@@ -375,7 +377,8 @@ def run_b200_arm(args):
 
     h2d = sum(t.numel() * t.element_size() for t in host[:2])
     if fused_info is None:
-        roofline = {"kernel": "flat_step_vec4<true,true> (mdb200_dot_step)", "bound": "hbm",
+        roofline = {"kernel": "flat_step_vec4<true,true> (mdb200_dot_step)" if is_dot
+                    else "flat_step_vec4<true,false> (mdb200_sgd_step)", "bound": "hbm",
                     "achieved": dot_bytes / dot_avg / 1e9, "peak": peak, "unit": "GB/s",
                     "frac": dot_bytes / dot_avg / 1e9 / peak, "traffic": profiled_traffic("dot_step", shard_elems),
                     "peak_source": peak_src, "bytes_per_launch": dot_bytes, "us_per_launch": dot_avg * 1e6,
