@@ -239,6 +239,11 @@ def kernel_sweep(dev):
         med, best = timed(lambda: ops.sgd_step(p, gt, vt, lr=0.05, momentum=0.9, weight_decay=5e-4))
         out[tag.replace("dot_", "sgd_")] = {"us": med * 1e6, "GB/s": 20 * n / med / 1e9,
                                             "frac_of_measured_peak": 20 * n / med / 1e9 / peak, "bytes": 20 * n}
+        vk.fill_(1e-3)
+        med, best = timed(lambda: ops.adam_step(p, gt, vt, vk, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8,
+                                                weight_decay=1e-4, step=10))
+        out[tag.replace("dot_", "adam_")] = {"us": med * 1e6, "GB/s": 28 * n / med / 1e9,
+                                             "frac_of_measured_peak": 28 * n / med / 1e9 / peak, "bytes": 28 * n}
     return out
 
 

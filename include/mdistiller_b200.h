@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define MDB200_ABI_VERSION 1
+#define MDB200_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define MDB200_API __attribute__((visibility("default")))
@@ -196,11 +196,41 @@ MDB200_API int mdb200_dot_step_fused(float *p_local, float *p_multicast, float *
  * Single-momentum SGD on a flat range, in place: torch.optim.SGD(momentum,
  * weight_decay, dampening, nesterov=False) as built by BaseTrainer.init_optimizer
  * (mdistiller/engine/trainer.py:86-91) and stepped at trainer.py:321.
- * v may be NULL when momentum == 0.  20 algorithmic bytes per element.
+ * v may be NULL when momentum == 0.  grad_scale_dev (may be NULL) points at one float on
+ * the device that also multiplies the gradient -- the clipping coefficient of
+ * mdb200_clip_coefficient.  20 algorithmic bytes per element.
  */
 MDB200_API int mdb200_sgd_step(float *p, const float *g, float *v, int64_t n,
                     float lr, float momentum, float weight_decay, float dampening,
-                    float grad_scale, int first_step, void *stream);
+                    float grad_scale, const float *grad_scale_dev, int first_step, void *stream);
+
+/*
+ * Adam / AdamW on a flat range, in place: torch.optim.Adam / AdamW (no amsgrad) as built by
+ * BaseTrainer.init_optimizer (mdistiller/engine/trainer.py:92-107, SOLVER.TYPE "Adam" /
+ * "AdamW", configs/imagenet/optim/*.yaml) and stepped at trainer.py:321.  `step` is the
+ * 1-based step count (bias corrections 1 - beta^step are formed in double on the host side
+ * of this call, like torch's Python floats).  decoupled != 0 selects AdamW's
+ * p *= 1 - lr*wd; otherwise weight decay joins the gradient.  m, v: first and second moment.
+ * The betas are doubles so that 1 - beta2 keeps the precision torch's Python floats give it.
+ * 28 algorithmic bytes per element.
+ */
+MDB200_API int mdb200_adam_step(float *p, const float *g, float *m, float *v, int64_t n,
+                    float lr, double beta1, double beta2, float eps, float weight_decay, int decoupled,
+                    int64_t step, float grad_scale, const float *grad_scale_dev, void *stream);
+
+/*
+ * Gradient clipping by global norm, nn.utils.clip_grad_norm_ at mdistiller/engine/trainer.py:316-320,
+ * in two device-side pieces so the host never reads the norm:
+ *   mdb200_sum_squares      *out = sum over [0, n) of (scale * x[i])^2 in fp64, fixed summation
+ *                           order; workspace >= 64 + 1024*8 bytes, first 64 bytes zero before the
+ *                           first call (the loss workspace qualifies)
+ *   (host code all-reduces *out over ranks when the gradient is sharded)
+ *   mdb200_clip_coefficient *coef = min(1, max_norm / (sqrt(*total_sumsq) + 1e-6))
+ * and the step kernels take `coef` as grad_scale_dev.
+ */
+MDB200_API int mdb200_sum_squares(const float *x, int64_t n, float scale, double *out,
+                    void *workspace, size_t workspace_bytes, void *stream);
+MDB200_API int mdb200_clip_coefficient(const double *total_sumsq, float max_norm, float *coef, void *stream);
 
 #ifdef __cplusplus
 }

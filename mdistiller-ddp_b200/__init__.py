@@ -11,7 +11,7 @@ from .build import LIB_PATH, build as build_library  # noqa: F401
 from . import ops  # noqa: F401
 from .losses import dkd_loss, kd_loss, distill_tail, TailResult  # noqa: F401
 from .distillers import Distiller, DKD, KD  # noqa: F401
-from .optim import DistillationOrientedTrainer, FlatSGD  # noqa: F401
+from .optim import DistillationOrientedTrainer, FlatAdam, FlatSGD  # noqa: F401
 from .comm import ShardComm  # noqa: F401
 from .flat import FlatSpace  # noqa: F401
 from .trainer import TailStepMixin, StandaloneTrainer, new_train_meters, silence_ddp_reducer  # noqa: F401
@@ -21,7 +21,7 @@ distiller_dict = {"DKD": DKD, "KD": KD}
 
 __all__ = [
     "dkd_loss", "kd_loss", "distill_tail", "TailResult", "Distiller", "DKD", "KD",
-    "DistillationOrientedTrainer", "FlatSGD", "ShardComm", "FlatSpace", "TailStepMixin",
+    "DistillationOrientedTrainer", "FlatSGD", "FlatAdam", "ShardComm", "FlatSpace", "TailStepMixin",
     "StandaloneTrainer", "new_train_meters", "silence_ddp_reducer", "install", "uninstall", "distiller_dict",
     "build_library", "LIB_PATH", "ops",
 ]

@@ -48,7 +48,9 @@ constexpr int kStepUnroll = 2;  // float4 slots per thread per trip: 10 independ
 template <bool TASK, bool KD>
 __global__ void __launch_bounds__(kStepThreads) flat_step_vec4(float4 *__restrict__ p, const float4 *__restrict__ gt,
                                                                const float4 *__restrict__ gk, float4 *__restrict__ vt,
-                                                               float4 *__restrict__ vk, long long n4, const StepCoef c) {
+                                                               float4 *__restrict__ vk, long long n4, StepCoef c,
+                                                               const float *__restrict__ gs_dev) {
+    if (gs_dev) c.gscale *= __ldg(gs_dev);   // device-side factor (gradient-clipping coefficient)
     const long long tile = (long long)kStepThreads * kStepUnroll;
     const bool use_vt = TASK && !c.bypass_task;
     for (long long t0 = (long long)blockIdx.x * tile; t0 < n4; t0 += (long long)gridDim.x * tile) {
@@ -83,7 +85,8 @@ __global__ void __launch_bounds__(kStepThreads) flat_step_vec4(float4 *__restric
 // Scalar path: unaligned ranges and the < 4 element tail of the vector path.
 template <bool TASK, bool KD>
 __global__ void __launch_bounds__(kStepThreads) flat_step_scalar(float *p, const float *gt, const float *gk, float *vt,
-                                                                 float *vk, long long n, const StepCoef c) {
+                                                                 float *vk, long long n, StepCoef c, const float *gs_dev) {
+    if (gs_dev) c.gscale *= __ldg(gs_dev);
     const bool use_vt = TASK && !c.bypass_task;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
         float P = p[i], GT = TASK ? gt[i] : 0.f, GK = KD ? gk[i] : 0.f;
@@ -98,7 +101,7 @@ __global__ void __launch_bounds__(kStepThreads) flat_step_scalar(float *p, const
 
 template <bool TASK, bool KD>
 static cudaError_t launch_step(float *p, const float *gt, const float *gk, float *vt, float *vk, long long n,
-                               const StepCoef &c, cudaStream_t st) {
+                               const StepCoef &c, cudaStream_t st, const float *gs_dev = nullptr) {
     const bool vec = aligned16(p) && (!TASK || aligned16(gt)) && (!KD || aligned16(gk)) &&
                      (!(TASK && !c.bypass_task) || aligned16(vt)) && (!KD || aligned16(vk));
     const int sms = sm_count();
@@ -111,7 +114,7 @@ static cudaError_t launch_step(float *p, const float *gt, const float *gk, float
         if (blocks > cap) blocks = cap;
         flat_step_vec4<TASK, KD><<<(unsigned)blocks, kStepThreads, 0, st>>>(
             reinterpret_cast<float4 *>(p), reinterpret_cast<const float4 *>(gt), reinterpret_cast<const float4 *>(gk),
-            reinterpret_cast<float4 *>(vt), reinterpret_cast<float4 *>(vk), n4, c);
+            reinterpret_cast<float4 *>(vt), reinterpret_cast<float4 *>(vk), n4, c, gs_dev);
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) return e;
         done = n4 << 2;
@@ -123,7 +126,7 @@ static cudaError_t launch_step(float *p, const float *gt, const float *gk, float
         if (blocks > cap) blocks = cap;
         flat_step_scalar<TASK, KD><<<(unsigned)blocks, kStepThreads, 0, st>>>(
             p + done, TASK ? gt + done : nullptr, KD ? gk + done : nullptr, vt ? vt + done : nullptr,
-            vk ? vk + done : nullptr, rem, c);
+            vk ? vk + done : nullptr, rem, c, gs_dev);
         return cudaGetLastError();
     }
     return cudaSuccess;
@@ -167,7 +170,8 @@ extern "C" int mdb200_dot_step(float *p, const float *g_task, const float *g_kd,
 }
 
 extern "C" int mdb200_sgd_step(float *p, const float *g, float *v, int64_t n, float lr, float momentum,
-                               float weight_decay, float dampening, float grad_scale, int first_step, void *stream) {
+                               float weight_decay, float dampening, float grad_scale, const float *grad_scale_dev,
+                               int first_step, void *stream) {
     if (!p || !g || n < 0) return MDB200_EINVAL;
     if (momentum != 0.f && !v) return MDB200_EINVAL;
     if (!aligned4(p) || !aligned4(g)) return MDB200_EALIGN;
@@ -183,5 +187,6 @@ extern "C" int mdb200_sgd_step(float *p, const float *g, float *v, int64_t n, fl
     c.first_task = first_step != 0;
     c.first_kd = 0;
     c.bypass_task = momentum == 0.f;
-    return (int)launch_step<true, false>(p, g, nullptr, v, nullptr, n, c, reinterpret_cast<cudaStream_t>(stream));
+    return (int)launch_step<true, false>(p, g, nullptr, v, nullptr, n, c, reinterpret_cast<cudaStream_t>(stream),
+                                         grad_scale_dev);
 }

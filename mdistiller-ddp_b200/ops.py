@@ -136,17 +136,70 @@ def dot_step(p: torch.Tensor, g_task: Optional[torch.Tensor], g_kd: Optional[tor
 
 def sgd_step(p: torch.Tensor, g: torch.Tensor, v: Optional[torch.Tensor], *, lr: float, momentum: float,
              weight_decay: float = 0.0, dampening: float = 0.0, grad_scale: float = 1.0,
-             first_step: bool = False, n: Optional[int] = None) -> None:
+             first_step: bool = False, n: Optional[int] = None,
+             grad_scale_dev: Optional[torch.Tensor] = None) -> None:
     """In-place momentum-SGD update of the flat range p[:n]."""
     global launch_count
     lib = _lib.load()
     n = p.numel() if n is None else n
     ptrs = (_flat_ptr(p, "p", n), _flat_ptr(g, "g", n), _flat_ptr(v, "v", n))
+    gs = _flat_ptr(grad_scale_dev, "grad_scale_dev", 1)
     with torch.cuda.device(p.device):
-        rc = lib.mdb200_sgd_step(*ptrs, n, lr, momentum, weight_decay, dampening, grad_scale, int(first_step),
+        rc = lib.mdb200_sgd_step(*ptrs, n, lr, momentum, weight_decay, dampening, grad_scale, gs, int(first_step),
                                  _stream_ptr(p.device))
     _lib.check(rc, "mdb200_sgd_step")
     launch_count += 1
+
+
+def adam_step(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, *, lr: float, beta1: float,
+              beta2: float, eps: float, weight_decay: float = 0.0, decoupled: bool = False, step: int = 1,
+              grad_scale: float = 1.0, grad_scale_dev: Optional[torch.Tensor] = None,
+              n: Optional[int] = None) -> None:
+    """In-place Adam / AdamW update of the flat range p[:n] (step is 1-based)."""
+    global launch_count
+    lib = _lib.load()
+    n = p.numel() if n is None else n
+    ptrs = (_flat_ptr(p, "p", n), _flat_ptr(g, "g", n), _flat_ptr(m, "m", n), _flat_ptr(v, "v", n))
+    gs = _flat_ptr(grad_scale_dev, "grad_scale_dev", 1)
+    with torch.cuda.device(p.device):
+        rc = lib.mdb200_adam_step(*ptrs, n, lr, beta1, beta2, eps, weight_decay, int(decoupled), int(step),
+                                  grad_scale, gs, _stream_ptr(p.device))
+    _lib.check(rc, "mdb200_adam_step")
+    launch_count += 1
+
+
+def sum_squares(x: torch.Tensor, scale: float = 1.0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """out (1 x float64 on the device) = sum((scale * x)^2), deterministic."""
+    global launch_count
+    lib = _lib.load()
+    _need_cuda_f32(x, "x")
+    if not x.is_contiguous():
+        raise ValueError("x must be contiguous")
+    if out is None:
+        out = torch.empty(1, dtype=torch.float64, device=x.device)
+    ws = loss_workspace(x.device)
+    with torch.cuda.device(x.device):
+        rc = lib.mdb200_sum_squares(x.data_ptr(), x.numel(), scale, out.data_ptr(), ws.data_ptr(), ws.numel(),
+                                    _stream_ptr(x.device))
+    _lib.check(rc, "mdb200_sum_squares")
+    launch_count += 1
+    return out
+
+
+def clip_coefficient(total_sumsq: torch.Tensor, max_norm: float, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """out (1 x float32) = min(1, max_norm / (sqrt(total_sumsq) + 1e-6)) -- clip_grad_norm_'s factor."""
+    global launch_count
+    lib = _lib.load()
+    if not total_sumsq.is_cuda or total_sumsq.dtype != torch.float64:
+        raise TypeError("total_sumsq must be a CUDA float64 tensor")
+    if out is None:
+        out = torch.empty(1, dtype=torch.float32, device=total_sumsq.device)
+    with torch.cuda.device(total_sumsq.device):
+        rc = lib.mdb200_clip_coefficient(total_sumsq.data_ptr(), max_norm, out.data_ptr(),
+                                         _stream_ptr(total_sumsq.device))
+    _lib.check(rc, "mdb200_clip_coefficient")
+    launch_count += 1
+    return out
 
 
 def dot_step_fused(p_local: torch.Tensor, g_task_local: torch.Tensor, g_kd_local: torch.Tensor,

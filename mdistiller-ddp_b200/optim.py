@@ -114,6 +114,17 @@ class _FlatOptimizer(Optimizer):
         self._run_cache[key] = runs
         return runs
 
+    def _clip_coefficient(self, bucket: torch.Tensor, max_norm: float) -> Optional[torch.Tensor]:
+        """Device scalar min(1, max_norm / (||g|| + 1e-6)) over ALL ranks' averaged gradient --
+        nn.utils.clip_grad_norm_ (trainer.py:316-320) without a host sync.  `bucket` holds this
+        rank's reduce-scattered SUM in its shard; the 1/world average is applied inside the norm."""
+        if not max_norm or max_norm <= 0:
+            return None
+        sp = self._space
+        sumsq = self._k.sum_squares(sp.shard(bucket), scale=1.0 / self._comm.world_size)
+        self._comm.all_reduce_sum(sumsq)
+        return self._k.clip_coefficient(sumsq, float(max_norm))
+
     @property
     def flat_params(self) -> torch.Tensor:
         return self._space.flat
@@ -321,6 +332,7 @@ class FlatSGD(_FlatOptimizer):
         super().__init__(params, defaults, comm, kernels)
         self._v = self._space.new_shard_buffer()
         self._has_v = [False] * len(self._space.params)
+        self.max_grad_norm = 0.0      # SOLVER.GRAD_CLIP; > 0 clips the global gradient norm inside step()
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -333,6 +345,7 @@ class FlatSGD(_FlatOptimizer):
         work = self._comm.reduce_scatter_sum(self._buckets["grad"], async_op=True)
         if work is not None:
             work.wait()
+        clip = self._clip_coefficient(self._buckets["grad"], self.max_grad_norm)
         momentum = group["momentum"]
         modes = [((_TASK if t else _NONE), t and not self._has_v[i], False) for i, t in enumerate(members)]
         sp = self._space
@@ -342,7 +355,7 @@ class FlatSGD(_FlatOptimizer):
                              self._v[a:b] if momentum != 0 else None,
                              lr=group["lr"], momentum=momentum, weight_decay=group["weight_decay"],
                              dampening=group["dampening"], grad_scale=1.0 / self._comm.world_size,
-                             first_step=first)
+                             first_step=first, grad_scale_dev=clip)
         self._comm.all_gather(sp.flat)
         if momentum != 0:
             for i, t in enumerate(members):
@@ -360,4 +373,78 @@ class FlatSGD(_FlatOptimizer):
     def load_state_dict(self, state_dict):
         super().load_state_dict(state_dict)
         self._import_state((("momentum_buffer", self._v, self._has_v),))
+        self._run_cache.clear()
+
+
+class FlatAdam(_FlatOptimizer):
+    """torch.optim.Adam / AdamW (no amsgrad) on the flat space -- what BaseTrainer.init_optimizer
+    builds for SOLVER.TYPE "Adam" / "AdamW" (mdistiller/engine/trainer.py:92-107), plus the sharded
+    gradient sync and optional global-norm clipping.  State layout in checkpoints follows torch:
+    ``step``, ``exp_avg``, ``exp_avg_sq`` per parameter."""
+
+    _bucket_names = ("grad",)
+
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0, *, decoupled=False,
+                 comm: Optional[ShardComm] = None, kernels=None):
+        if lr < 0.0:
+            raise ValueError("Invalid learning rate: {}".format(lr))
+        if eps < 0.0:
+            raise ValueError("Invalid epsilon value: {}".format(eps))
+        if not 0.0 <= betas[0] < 1.0:
+            raise ValueError("Invalid beta parameter at index 0: {}".format(betas[0]))
+        if not 0.0 <= betas[1] < 1.0:
+            raise ValueError("Invalid beta parameter at index 1: {}".format(betas[1]))
+        if weight_decay < 0.0:
+            raise ValueError("Invalid weight_decay value: {}".format(weight_decay))
+        defaults = dict(lr=lr, betas=tuple(betas), eps=eps, weight_decay=weight_decay)
+        super().__init__(params, defaults, comm, kernels)
+        self.decoupled = bool(decoupled)
+        self._m = self._space.new_shard_buffer()
+        self._v = self._space.new_shard_buffer()
+        self._steps = [0] * len(self._space.params)     # per parameter, like torch's state['step']
+        self.max_grad_norm = 0.0
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        group = self.param_groups[0]
+        members = self._collect("grad")
+        work = self._comm.reduce_scatter_sum(self._buckets["grad"], async_op=True)
+        if work is not None:
+            work.wait()
+        clip = self._clip_coefficient(self._buckets["grad"], self.max_grad_norm)
+        for i, t in enumerate(members):
+            if t:
+                self._steps[i] += 1
+        modes = [((_TASK if t else _NONE), self._steps[i], False) for i, t in enumerate(members)]
+        sp = self._space
+        b1, b2 = group["betas"]
+        for lo, hi, (_, step, _) in self._runs(modes):
+            a, b = lo - sp.shard_lo, hi - sp.shard_lo
+            self._k.adam_step(sp.flat[lo:hi], self._buckets["grad"][lo:hi], self._m[a:b], self._v[a:b],
+                              lr=group["lr"], beta1=b1, beta2=b2, eps=group["eps"],
+                              weight_decay=group["weight_decay"], decoupled=self.decoupled, step=step,
+                              grad_scale=1.0 / self._comm.world_size, grad_scale_dev=clip)
+        self._comm.all_gather(sp.flat)
+        return loss
+
+    def state_dict(self):
+        has = [n > 0 for n in self._steps]
+        self._export_state((("exp_avg", self._m, has), ("exp_avg_sq", self._v, has)))
+        for p, n in zip(self._space.params, self._steps):
+            if n > 0:
+                self.state[p]["step"] = torch.tensor(float(n))
+        try:
+            return super().state_dict()
+        finally:
+            self.state.clear()
+
+    def load_state_dict(self, state_dict):
+        super().load_state_dict(state_dict)
+        self._steps = [int(self.state.get(p, {}).get("step", 0)) for p in self._space.params]
+        has = [False] * len(self._steps)
+        self._import_state((("exp_avg", self._m, has), ("exp_avg_sq", self._v, list(has))))
         self._run_cache.clear()

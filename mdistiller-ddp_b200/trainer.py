@@ -23,7 +23,7 @@ import torch
 import torch.distributed as dist
 
 from .comm import ShardComm, SymmetricShardComm
-from .optim import DistillationOrientedTrainer, FlatSGD
+from .optim import DistillationOrientedTrainer, FlatAdam, FlatSGD
 
 
 def _unwrap(distiller):
@@ -84,13 +84,22 @@ class TailStepMixin:
                 momentum=cfg.SOLVER.SGD.MOMENTUM - cfg.SOLVER.DOT.DELTA,
                 momentum_kd=cfg.SOLVER.SGD.MOMENTUM + cfg.SOLVER.DOT.DELTA,
                 weight_decay=cfg.SOLVER.WEIGHT_DECAY, comm=comm)
-        if cfg.SOLVER.TYPE != "SGD":
-            raise NotImplementedError(f"{cfg.SOLVER.TYPE}: only the SGD solver has a flat sm_100a step")
         if cfg.EXPERIMENT.AMP:
-            raise NotImplementedError("AMP is outside the fp32 distillation tail")
+            raise NotImplementedError("AMP (autocast + GradScaler, trainer.py:304-313) is outside the fp32 "
+                                      "distillation tail")
         core.combined_tail = True     # one gradient buffer: the base trainer sums the losses anyway
-        return FlatSGD(params, lr=cfg.SOLVER.LR, momentum=cfg.SOLVER.SGD.MOMENTUM,
-                       weight_decay=cfg.SOLVER.WEIGHT_DECAY, comm=comm)
+        kind = cfg.SOLVER.TYPE
+        if kind == "SGD":
+            opt = FlatSGD(params, lr=cfg.SOLVER.LR, momentum=cfg.SOLVER.SGD.MOMENTUM,
+                          weight_decay=cfg.SOLVER.WEIGHT_DECAY, comm=comm)
+        elif kind in ("Adam", "AdamW"):
+            opt = FlatAdam(params, lr=cfg.SOLVER.LR, betas=tuple(cfg.SOLVER.ADAM.BETAS),
+                           eps=cfg.SOLVER.ADAM.EPSILON, weight_decay=cfg.SOLVER.WEIGHT_DECAY,
+                           decoupled=(kind == "AdamW"), comm=comm)
+        else:
+            raise NotImplementedError(kind)
+        opt.max_grad_norm = float(getattr(cfg.SOLVER, "GRAD_CLIP", 0.0) or 0.0)   # clip inside step(), on the shard
+        return opt
 
     # ---------------------------------------------------------------- one iteration
     def train_iter(self, data, epoch, train_meters):
@@ -131,9 +140,7 @@ class TailStepMixin:
                 torch.autograd.backward([tail.logits], [tail.grad_kd])
             else:
                 sum(losses.values()).backward()
-            if getattr(self, "grad_clip", 0.0) and self.grad_clip > 0:
-                raise NotImplementedError("SOLVER.GRAD_CLIP is not part of the flat step yet")
-            opt.step()
+            opt.step()        # SOLVER.GRAD_CLIP (trainer.py:316-320) happens inside, after the reduce-scatter
         if tail is not None:
             core.last_tail = None
         return preds, losses

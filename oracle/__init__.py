@@ -24,5 +24,7 @@ from .tail_oracle import (  # noqa: F401
     DotListOracle,
     dot_flat_step,
     sgd_flat_step,
+    adam_flat_step,
+    clip_coefficient,
     max_rel_err,
 )

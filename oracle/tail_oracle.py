@@ -306,6 +306,29 @@ def sgd_flat_step(p, g, v, *, lr, momentum, weight_decay, dampening=0.0,
     p.add_(d, alpha=-lr)
 
 
+def adam_flat_step(p, g, m, v, *, lr, beta1, beta2, eps, weight_decay=0.0, decoupled=False, step=1,
+                   grad_scale=1.0) -> None:
+    """torch.optim.Adam / AdamW single-tensor update (no amsgrad), in place, `step` 1-based --
+    the optimizers BaseTrainer.init_optimizer builds at mdistiller/engine/trainer.py:92-107."""
+    gg = g if grad_scale == 1.0 else g * grad_scale
+    if weight_decay != 0:
+        if decoupled:
+            p.mul_(1 - lr * weight_decay)
+        else:
+            gg = gg.add(p, alpha=weight_decay)
+    m.lerp_(gg, 1 - beta1)
+    v.mul_(beta2).addcmul_(gg, gg, value=1 - beta2)
+    bc1, bc2 = 1 - beta1 ** step, 1 - beta2 ** step
+    denom = (v.sqrt() / (bc2 ** 0.5)).add_(eps)
+    p.addcdiv_(m, denom, value=-(lr / bc1))
+
+
+def clip_coefficient(grads: Sequence[torch.Tensor], max_norm: float) -> float:
+    """nn.utils.clip_grad_norm_'s factor (mdistiller/engine/trainer.py:316-320): min(1, c / (||g||_2 + 1e-6))."""
+    total = torch.sqrt(sum((t.double() ** 2).sum() for t in grads if t is not None)).item()
+    return min(1.0, max_norm / (total + 1e-6))
+
+
 def max_rel_err(a, b) -> float:
     """The parity metric fixed in SURVEY.md section 7: max|a-b| / max|b| per tensor."""
     a = np.asarray(a.detach().cpu() if isinstance(a, torch.Tensor) else a, dtype=np.float64)

@@ -96,7 +96,8 @@ SMALL_SHAPES: List[Tuple[int, ...]] = [(16, 3, 3, 3), (16,), (16,), (24, 16, 3, 
 class DotCase:
     name: str
     seed: int
-    kind: str = "dot"                       # "dot" | "sgd"
+    kind: str = "dot"                       # "dot" | "sgd" | "adam" | "adamw"
+    clip: float = 0.0                       # SOLVER.GRAD_CLIP (global-norm clipping before the step)
     shapes: Tuple[Tuple[int, ...], ...] = tuple(SMALL_SHAPES)
     steps: int = 100
     lr: float = 0.05
@@ -121,7 +122,15 @@ DOT_CASES: List[DotCase] = [
     DotCase("dot_cifar_medium", 106, shapes=tuple(_cifar_like_shapes())),
     DotCase("sgd_cifar_small", 110, kind="sgd"),
     DotCase("sgd_medium", 111, kind="sgd", shapes=tuple(_cifar_like_shapes()), wd=1e-4, lr=0.2),
+    # optimizer-path variants of the base trainer (trainer.py:92-107, 316-320)
+    DotCase("sgd_clip_small", 112, kind="sgd", clip=0.5),
+    DotCase("adam_small", 113, kind="adam", lr=1e-3, wd=1e-4),
+    DotCase("adamw_small", 114, kind="adamw", lr=1e-3, wd=5e-2),
+    DotCase("adamw_clip_partial", 115, kind="adamw", lr=1e-3, wd=5e-2, clip=0.5, task_missing=frozenset({4})),
+    DotCase("adam_medium", 116, kind="adam", shapes=tuple(_cifar_like_shapes()), lr=1e-3, wd=0.0, steps=50),
 ]
+
+ADAM_BETAS, ADAM_EPS = (0.9, 0.999), 1e-8
 
 
 def make_params(case: DotCase) -> List[torch.Tensor]:

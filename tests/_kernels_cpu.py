@@ -60,8 +60,24 @@ class OracleKernels:
             v_kd.mul_(m_kd).add_(gk, alpha=1 - damp)
         p.add_(v_kd, alpha=-lr)
 
-    def sgd_step(self, p, g, v, *, lr, momentum, weight_decay, dampening, grad_scale, first_step, n=None):
+    def sgd_step(self, p, g, v, *, lr, momentum, weight_decay, dampening, grad_scale, first_step, n=None,
+                 grad_scale_dev=None):
         self.calls.append(("sgd", p.numel(), bool(first_step)))
+        gs = grad_scale * (float(grad_scale_dev.item()) if grad_scale_dev is not None else 1.0)
         oracle.sgd_flat_step(p, g, v if v is not None else torch.zeros_like(p), lr=lr, momentum=momentum,
                              weight_decay=weight_decay, dampening=dampening, first_step=first_step,
-                             grad_scale=grad_scale)
+                             grad_scale=gs)
+
+    def adam_step(self, p, g, m, v, *, lr, beta1, beta2, eps, weight_decay, decoupled, step, grad_scale,
+                  grad_scale_dev=None, n=None):
+        self.calls.append(("adam", p.numel(), int(step)))
+        gs = grad_scale * (float(grad_scale_dev.item()) if grad_scale_dev is not None else 1.0)
+        oracle.adam_flat_step(p, g, m, v, lr=lr, beta1=beta1, beta2=beta2, eps=eps, weight_decay=weight_decay,
+                              decoupled=decoupled, step=step, grad_scale=gs)
+
+    def sum_squares(self, x, scale=1.0, out=None):
+        return ((x.double() * scale) ** 2).sum().reshape(1)
+
+    def clip_coefficient(self, total_sumsq, max_norm, out=None):
+        norm = float(total_sumsq.sqrt().item())
+        return torch.tensor([min(1.0, max_norm / (norm + 1e-6))], dtype=torch.float32)

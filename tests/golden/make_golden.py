@@ -103,17 +103,27 @@ def _run_ref_dot(case, dtype):
 
 
 def _run_ref_sgd(case, dtype):
+    """torch.optim.{SGD,Adam,AdamW} (+ clip_grad_norm_) exactly as BaseTrainer drives them
+    (mdistiller/engine/trainer.py:86-107, 316-321)."""
     params = [p.to(dtype).clone().requires_grad_(True) for p in _cases.make_params(case)]
-    opt = torch.optim.SGD(params, lr=case.lr, momentum=case.momentum, weight_decay=case.wd,
-                          dampening=case.dampening)
+    if case.kind == "sgd":
+        opt = torch.optim.SGD(params, lr=case.lr, momentum=case.momentum, weight_decay=case.wd,
+                              dampening=case.dampening)
+    else:
+        cls = torch.optim.Adam if case.kind == "adam" else torch.optim.AdamW
+        opt = cls(params, lr=case.lr, betas=_cases.ADAM_BETAS, eps=_cases.ADAM_EPS, weight_decay=case.wd)
     for step in range(case.steps):
         if step == case.lr_drop_at:
             opt.param_groups[0]["lr"] = case.lr * 0.1
         _, g_task = _cases.make_grads(case, step, [p.shape for p in params])
         for p, g in zip(params, g_task):
             p.grad = None if g is None else g.to(dtype).clone()
+        if case.clip > 0:
+            torch.nn.utils.clip_grad_norm_(params, case.clip)
         opt.step()
-    return params, [opt.state[p].get("momentum_buffer") for p in params]
+    key1 = "momentum_buffer" if case.kind == "sgd" else "exp_avg"
+    second = [opt.state[p].get("exp_avg_sq") for p in params]
+    return params, [opt.state[p].get(key1) for p in params], second
 
 
 def _flat(ts, like):
@@ -131,8 +141,7 @@ def dot_fixture():
             if case.kind == "dot":
                 params, bt, bk = _run_ref_dot(case, dt)
             else:
-                params, bt = _run_ref_sgd(case, dt)
-                bk = [None] * len(params)
+                params, bt, bk = _run_ref_sgd(case, dt)      # (momentum | exp_avg, exp_avg_sq)
             flat_p = _flat(params, params)
             flat_t = _flat(bt, params)
             flat_k = _flat(bk, params)

@@ -30,7 +30,8 @@ def lib():
 def test_header_declares_the_expected_surface():
     assert set(_declared()) >= {"mdb200_abi_version", "mdb200_error_string", "mdb200_loss_workspace_bytes",
                                 "mdb200_distill_loss", "mdb200_scale_by_device_scalar", "mdb200_dot_step",
-                                "mdb200_sgd_step", "mdb200_dot_step_fused", "mdb200_distill_loss_static_scratch"}
+                                "mdb200_sgd_step", "mdb200_dot_step_fused", "mdb200_distill_loss_static_scratch",
+                                "mdb200_adam_step", "mdb200_sum_squares", "mdb200_clip_coefficient"}
 
 
 def test_every_declared_symbol_is_exported_and_bound(lib):
@@ -41,7 +42,7 @@ def test_every_declared_symbol_is_exported_and_bound(lib):
 
 
 def test_version_and_error_strings(lib):
-    assert lib.mdb200_abi_version() == 1
+    assert lib.mdb200_abi_version() == 2
     assert lib.mdb200_error_string(0) == b"ok"
     assert b"workspace" in lib.mdb200_error_string(-3)
     assert lib.mdb200_loss_workspace_bytes() >= 64 + 2 * 8 * 1184
@@ -63,7 +64,7 @@ def test_argument_errors_are_reported_before_any_cuda_work(lib):
     assert lib.mdb200_dot_step(None, None, None, None, None, 16, .1, .9, .9, 0., 0., 1., 0, 0, 0, None) == -1
     assert lib.mdb200_dot_step(p, p, p, p, p, 16, .1, .9, .9, 0., 0., 1., 0, 0, 9, None) == -1
     assert lib.mdb200_dot_step(p, p, p, p, p, 0, .1, .9, .9, 0., 0., 1., 0, 0, 0, None) == 0   # empty range
-    assert lib.mdb200_sgd_step(p, p, None, 16, .1, .9, 0., 0., 1., 0, None) == -1            # momentum needs v
+    assert lib.mdb200_sgd_step(p, p, None, 16, .1, .9, 0., 0., 1., None, 0, None) == -1            # momentum needs v
     fused = lambda **kw: lib.mdb200_dot_step_fused(  # noqa: E731
         kw.get("p", p), None, None, p, None, None, p, None, None, 1, p, p, kw.get("lo", 0), kw.get("n", 16),
         kw.get("world", 2), .1, .9, .9, 0., 0., .5, 0, 0, None)
@@ -71,6 +72,9 @@ def test_argument_errors_are_reported_before_any_cuda_work(lib):
     assert fused(world=17) == -1               # more peers than the kernel addresses
     assert fused(lo=2) == -4                   # shard must start on a 16-byte slot
     assert fused(p=None) == -1
+    assert lib.mdb200_adam_step(p, p, p, p, 16, 1e-3, .9, .999, 1e-8, 0., 0, 0, 1., None, None) == -1   # step is 1-based
+    assert lib.mdb200_sum_squares(p, 16, 1., p, p, 16, None) == -3
+    assert lib.mdb200_clip_coefficient(p, 0., p, None) == -1
     assert lib.mdb200_distill_loss_static_scratch(None, None, None, 4, 8, 8, 8, 0, 1., 1., 1., 1., 0, 1.,
                                                   None, None, 8, None, None) == -1
 

@@ -59,10 +59,17 @@ def test_100_step_trajectory_matches_reference(case, dot_golden, b200):
             assert oracle.max_rel_err(got, ref) <= TOL, (case.name, key, tag)
 
 
-@pytest.mark.parametrize("case", [c for c in _cases.DOT_CASES if c.kind == "sgd"], ids=lambda c: c.name)
-def test_sgd_trajectory_matches_torch_sgd(case, dot_golden, b200):
+@pytest.mark.parametrize("case", [c for c in _cases.DOT_CASES if c.kind != "dot"], ids=lambda c: c.name)
+def test_base_optimizer_trajectories_match_torch(case, dot_golden, b200):
+    """SGD / Adam / AdamW with and without global-norm clipping vs torch.optim + clip_grad_norm_
+    (what BaseTrainer runs, trainer.py:86-107, 316-321)."""
     params = [torch.nn.Parameter(p.clone().cuda()) for p in _cases.make_params(case)]
-    opt = b200.FlatSGD(params, lr=case.lr, momentum=case.momentum, weight_decay=case.wd, dampening=case.dampening)
+    if case.kind == "sgd":
+        opt = b200.FlatSGD(params, lr=case.lr, momentum=case.momentum, weight_decay=case.wd, dampening=case.dampening)
+    else:
+        opt = b200.FlatAdam(params, lr=case.lr, betas=_cases.ADAM_BETAS, eps=_cases.ADAM_EPS, weight_decay=case.wd,
+                            decoupled=(case.kind == "adamw"))
+    opt.max_grad_norm = case.clip
     shapes = [p.shape for p in params]
     for step in range(case.steps):
         if step == case.lr_drop_at:
@@ -70,10 +77,28 @@ def test_sgd_trajectory_matches_torch_sgd(case, dot_golden, b200):
         _, task = _cases.make_grads(case, step, shapes)
         opt.zero_grad()
         for p, g in zip(params, task):
-            p.grad = g.cuda()
+            p.grad = None if g is None else g.cuda()
         opt.step()
     got, ref = _ref(dot_golden, case.name, "p64", _flat(params, params))
     assert oracle.max_rel_err(got, ref) <= TOL
+    if case.kind != "sgd":
+        sp = opt._space
+        for key, buf in (("vt64", opt._m), ("vk64", opt._v)):       # exp_avg, exp_avg_sq
+            got, ref = _ref(dot_golden, case.name, key, _flat(sp.views(buf), params))
+            assert oracle.max_rel_err(got, ref) <= TOL
+
+
+def test_sum_squares_and_clip_coefficient(b200):
+    ops = b200.ops
+    for n in (5, 4099, 11_689_512):
+        x = torch.randn(n, device="cuda") * 0.3
+        want = (x.double() * 0.125).pow(2).sum().item()
+        got = ops.sum_squares(x, scale=0.125)
+        assert abs(got.item() - want) <= 1e-6 * want
+        assert torch.equal(got, ops.sum_squares(x, scale=0.125))          # fixed summation order
+        for max_norm in (0.01, 1e6):
+            c = ops.clip_coefficient(got, max_norm).item()
+            assert abs(c - min(1.0, max_norm / (want ** 0.5 + 1e-6))) <= 1e-6
 
 
 @pytest.mark.parametrize("n", [11_689_512, 25_557_032, 1_000_003, 5])

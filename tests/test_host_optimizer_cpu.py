@@ -174,12 +174,23 @@ def test_reference_optimizer_state_dict_loads_into_ours():
         assert torch.equal(p.detach(), q.detach())
 
 
-@pytest.mark.parametrize("case", [c for c in _cases.DOT_CASES if c.kind == "sgd" and len(c.shapes) < 20],
+def _make_base_optimizer(case, params, **kw):
+    if case.kind == "sgd":
+        opt = b200.FlatSGD(params, lr=case.lr, momentum=case.momentum, weight_decay=case.wd,
+                           dampening=case.dampening, **kw)
+    else:
+        opt = b200.FlatAdam(params, lr=case.lr, betas=_cases.ADAM_BETAS, eps=_cases.ADAM_EPS, weight_decay=case.wd,
+                            decoupled=(case.kind == "adamw"), **kw)
+    opt.max_grad_norm = case.clip
+    return opt
+
+
+@pytest.mark.parametrize("case", [c for c in _cases.DOT_CASES if c.kind != "dot" and len(c.shapes) < 20],
                          ids=lambda c: c.name)
-def test_flat_sgd_reproduces_torch_sgd(case, dot_golden):
+def test_flat_base_optimizers_reproduce_torch(case, dot_golden):
+    """SGD / Adam / AdamW (+ global-norm clipping) as the base trainer drives them (trainer.py:86-107,316-321)."""
     params = [torch.nn.Parameter(p.clone()) for p in _cases.make_params(case)]
-    opt = b200.FlatSGD(params, lr=case.lr, momentum=case.momentum, weight_decay=case.wd,
-                       dampening=case.dampening, kernels=OracleKernels())
+    opt = _make_base_optimizer(case, params, kernels=OracleKernels())
     shapes = [p.shape for p in params]
     for step in range(case.steps):
         if step == case.lr_drop_at:
@@ -187,9 +198,19 @@ def test_flat_sgd_reproduces_torch_sgd(case, dot_golden):
         _, task = _cases.make_grads(case, step, shapes)
         opt.zero_grad()
         for p, g in zip(params, task):
-            p.grad = g.clone()
+            p.grad = None if g is None else g.clone()
         opt.step()
-    assert oracle.max_rel_err(_flat(params, params), dot_golden[f"{case.name}/p32"]) <= 1e-6
+    assert oracle.max_rel_err(_flat(params, params), dot_golden[f"{case.name}/p32"]) <= 2e-6
+    if case.kind != "sgd":       # checkpoint layout follows torch.optim.Adam: step / exp_avg / exp_avg_sq
+        sd = opt.state_dict()
+        assert set(sd["state"][0]) == {"step", "exp_avg", "exp_avg_sq"} and float(sd["state"][0]["step"]) == case.steps
+        assert 4 not in sd["state"] or 4 not in case.task_missing
+        ref = torch.optim.AdamW(params, lr=1.0) if case.kind == "adamw" else torch.optim.Adam(params, lr=1.0)
+        ref.load_state_dict(sd)                      # torch's own class accepts our checkpoint
+        assert ref.param_groups[0]["lr"] == pytest.approx(case.lr * 0.1)
+        opt2 = _make_base_optimizer(case, [torch.nn.Parameter(p.detach().clone()) for p in params], kernels=OracleKernels())
+        opt2.load_state_dict(sd)
+        assert opt2._steps == opt._steps and torch.equal(opt2._m, opt._m) and torch.equal(opt2._v, opt._v)
 
 
 # ---------------------------------------------------------------------------- world_size 2, gloo
@@ -277,3 +298,45 @@ def test_sharded_step_world2_matches_single_process_on_averaged_gradients(case_i
             assert oracle.max_rel_err(st[i]["momentum_kd_buffer"], ref.buf_kd[i]) <= 2e-6
         if ref.buf_task[i] is not None:
             assert oracle.max_rel_err(st[i]["momentum_buffer"], ref.buf_task[i]) <= 2e-6
+
+
+def _base_worker(rank, world, port, case_idx, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        case = _cases.DOT_CASES[case_idx]
+        params = [torch.nn.Parameter(p.clone()) for p in _cases.make_params(case)]
+        opt = _make_base_optimizer(case, params, comm=GlooShardComm(), kernels=OracleKernels())
+        shapes = [p.shape for p in params]
+        sign = 1.0 if rank == 0 else -1.0
+        for step in range(15):
+            _, task = _cases.make_grads(case, step, shapes)
+            opt.zero_grad()
+            for p, g in zip(params, task):
+                p.grad = None if g is None else g * (1.0 + 0.5 * sign)     # mean over the two ranks = g
+            opt.step()
+        if rank == 0:
+            torch.save([p.detach().clone() for p in params], out)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("name", ["sgd_clip_small", "adamw_clip_partial"])
+def test_sharded_base_optimizers_with_clipping_world2(name, tmp_path):
+    """The clipping norm is global: per-shard sums of squares of the rank-averaged gradient, all-reduced."""
+    case_idx = [c.name for c in _cases.DOT_CASES].index(name)
+    case = _cases.DOT_CASES[case_idx]
+    out = str(tmp_path / "r0.pt")
+    mp.spawn(_base_worker, args=(2, 29300 + (os.getpid() % 500) + case_idx, case_idx, out), nprocs=2, join=True)
+    got = torch.load(out, weights_only=False)
+    params = [torch.nn.Parameter(p.clone()) for p in _cases.make_params(case)]
+    ref = _make_base_optimizer(case, params, kernels=OracleKernels())
+    shapes = [p.shape for p in params]
+    for step in range(15):
+        _, task = _cases.make_grads(case, step, shapes)
+        ref.zero_grad()
+        for p, g in zip(params, task):
+            p.grad = None if g is None else g.clone()
+        ref.step()
+    for p, q in zip(got, params):
+        assert oracle.max_rel_err(p, q) <= 2e-6

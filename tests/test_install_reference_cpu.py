@@ -92,6 +92,10 @@ def test_reference_base_trainer_gets_flat_sgd(patched):
     trainer = E.trainer_dict["base"]("exp2", distiller, [], [], cfg)
     assert isinstance(trainer.optimizer, b200.FlatSGD) and distiller.combined_tail
     assert trainer.optimizer.param_groups[0]["momentum"] == cfg.SOLVER.SGD.MOMENTUM
-    cfg.SOLVER.TYPE = "Adam"
+    cfg.SOLVER.TYPE, cfg.SOLVER.GRAD_CLIP = "AdamW", 1.0          # configs/imagenet/optim/adamw.yaml
+    tr = E.trainer_dict["base"]("exp3", distiller, [], [], cfg)
+    assert isinstance(tr.optimizer, b200.FlatAdam) and tr.optimizer.decoupled and tr.optimizer.max_grad_norm == 1.0
+    assert tr.optimizer.param_groups[0]["betas"] == tuple(cfg.SOLVER.ADAM.BETAS)
+    cfg.EXPERIMENT.AMP = True
     with pytest.raises(NotImplementedError):
-        E.trainer_dict["base"]("exp3", distiller, [], [], cfg)
+        E.trainer_dict["base"]("exp4", distiller, [], [], cfg)

@@ -100,17 +100,34 @@ def _run_oracle_lists(case, dtype):
             opt.step_kd([None if g is None else g.to(dtype) for g in kd])
             opt.step([None if g is None else g.to(dtype) for g in task])
         return params, opt.buf_task, opt.buf_kd
-    flat_p = torch.cat([p.reshape(-1) for p in params])
-    v = torch.zeros_like(flat_p)
+    # base-trainer optimizers, tensor by tensor like torch does (parameters without a gradient are skipped)
+    first = [None] * len(params)
+    second = [None] * len(params)
+    steps = [0] * len(params)
     lr = case.lr
     for step in range(case.steps):
         if step == case.lr_drop_at:
             lr = case.lr * 0.1
         _, task = _cases.make_grads(case, step, shapes)
-        g = torch.cat([t.to(dtype).reshape(-1) for t in task])
-        oracle.sgd_flat_step(flat_p, g, v, lr=lr, momentum=case.momentum, weight_decay=case.wd,
-                             dampening=case.dampening, first_step=(step == 0))
-    return [flat_p], [v], [None]
+        task = [None if g is None else g.to(dtype) for g in task]
+        coef = oracle.clip_coefficient(task, case.clip) if case.clip > 0 else 1.0
+        for i, (p, g) in enumerate(zip(params, task)):
+            if g is None:
+                continue
+            steps[i] += 1
+            if case.kind == "sgd":
+                fresh = first[i] is None
+                if fresh:
+                    first[i] = torch.zeros_like(p)
+                oracle.sgd_flat_step(p, g, first[i], lr=lr, momentum=case.momentum, weight_decay=case.wd,
+                                     dampening=case.dampening, first_step=fresh, grad_scale=coef)
+            else:
+                if first[i] is None:
+                    first[i], second[i] = torch.zeros_like(p), torch.zeros_like(p)
+                oracle.adam_flat_step(p, g, first[i], second[i], lr=lr, beta1=_cases.ADAM_BETAS[0],
+                                      beta2=_cases.ADAM_BETAS[1], eps=_cases.ADAM_EPS, weight_decay=case.wd,
+                                      decoupled=(case.kind == "adamw"), step=steps[i], grad_scale=coef)
+    return params, first, second
 
 
 def _flat(ts, like):
