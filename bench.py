@@ -247,6 +247,52 @@ def kernel_sweep(dev):
     return out
 
 
+def torch_on_gpu_baseline(dev):
+    """What the kernels displace ON THE SAME GPU: the reference's torch
+    formulation -- the oracle restatement of dkd_loss + autograd, and the per-tensor DOT loop -- run
+    on CUDA tensors.  A baseline leg like cpu_baseline: never part of the product path."""
+    import oracle
+    import torchvision.models as tvm
+    out = {}
+
+    def timed(fn, reps=5):
+        fn()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(reps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            b.synchronize()
+            ts.append(a.elapsed_time(b) * 1e-3)
+        return statistics.median(ts)
+
+    for B, C, T, beta in ((256, 1000, 1.0, 0.5), (65536, 1000, 1.0, 0.5)):
+        zs = (torch.randn(B, C, device=dev) * 3).requires_grad_(True)
+        zt = torch.randn(B, C, device=dev) * 3
+        y = torch.randint(0, C, (B,), device=dev)
+
+        def ref_loss():
+            zs.grad = None
+            (oracle.dkd_loss(zs, zt, y, 1.0, beta, T) + oracle.ce_loss(zs, y)).backward()
+        t = timed(ref_loss)
+        out[f"torch_dkd+ce_fwd_bwd_{B}x{C}"] = {"us": t * 1e6, "algorithmic_GB/s": (12 * B * C) / t / 1e9}
+        del zs, zt
+    params = [p.detach().clone().to(dev) for p in tvm.resnet18(weights=None).parameters()]
+    opt = oracle.DotListOracle(params, lr=0.2, momentum=0.81, momentum_kd=0.99, weight_decay=1e-4)
+    g1 = [torch.randn_like(p) * 0.1 for p in params]
+    g2 = [torch.randn_like(p) * 0.1 for p in params]
+
+    def ref_dot():
+        opt.step_kd(g1)
+        opt.step(g2)
+    t = timed(ref_dot, reps=10)
+    n = sum(p.numel() for p in params)
+    out["torch_dot_step_resnet18_62_tensors"] = {"us": t * 1e6, "algorithmic_GB/s": 32 * n / t / 1e9}
+    return out
+
+
 def run_b200_arm(args):
     import torch.distributed as dist
     import mdistiller_ddp_b200 as b200
@@ -432,6 +478,8 @@ def run_b200_arm(args):
     }
     if not args.no_sweep:
         line["kernels"] = kernel_sweep(dev)
+        if world == 1:
+            line["torch_on_b200_baseline"] = torch_on_gpu_baseline(dev)
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = {k: v for k, v in cpu_arm(args.workload, args.cpu_batch, 8, 1).items()
                                 if k != "ms_per_step"}
