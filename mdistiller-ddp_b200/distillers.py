@@ -69,7 +69,10 @@ class Distiller(nn.Module):
         return logits_student, logits_teacher
 
     def _tail(self, logits_student, logits_teacher, target, **kw):
-        loss_kd, loss_ce, res = distill_tail(logits_student, logits_teacher, target,
+        # the tail computes in fp32 like the reference's softmax / cross_entropy do under autocast
+        # (trainer.py:268 wraps only the forward); fp32 logits pass through untouched
+        logits_fp32, logits_teacher = logits_student.float(), logits_teacher.float()
+        loss_kd, loss_ce, res = distill_tail(logits_fp32, logits_teacher, target,
                                              combined=self.combined_tail, **kw)
         self.last_tail = res
         return logits_student, {"loss_ce": loss_ce, "loss_kd": loss_kd}

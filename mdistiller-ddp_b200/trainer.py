@@ -84,10 +84,11 @@ class TailStepMixin:
                 momentum=cfg.SOLVER.SGD.MOMENTUM - cfg.SOLVER.DOT.DELTA,
                 momentum_kd=cfg.SOLVER.SGD.MOMENTUM + cfg.SOLVER.DOT.DELTA,
                 weight_decay=cfg.SOLVER.WEIGHT_DECAY, comm=comm)
-        if cfg.EXPERIMENT.AMP:
-            raise NotImplementedError("AMP (autocast + GradScaler, trainer.py:304-313) is outside the fp32 "
-                                      "distillation tail")
-        core.combined_tail = True     # one gradient buffer: the base trainer sums the losses anyway
+        # AMP (trainer.py:79-80, 268, 304-313): autocast forward + torch's GradScaler around our step; the
+        # scaled loss then has to go through autograd, so the pre-combined gradient shortcut is off
+        self.use_amp = bool(cfg.EXPERIMENT.AMP)
+        self.amp_scaler = torch.amp.GradScaler("cuda") if self.use_amp else None
+        core.combined_tail = not self.use_amp     # one gradient buffer: the base trainer sums the losses anyway
         kind = cfg.SOLVER.TYPE
         if kind == "SGD":
             opt = FlatSGD(params, lr=cfg.SOLVER.LR, momentum=cfg.SOLVER.SGD.MOMENTUM,
@@ -132,6 +133,21 @@ class TailStepMixin:
                 opt.zero_grad(set_to_none=True)
                 losses["loss_ce"].backward()
             opt.step()
+        elif getattr(self, "use_amp", False):
+            opt.zero_grad()
+            with torch.autocast("cuda"):
+                preds, losses = self.distiller(image=image, target=target, epoch=epoch)
+            tail = getattr(core, "last_tail", None)
+            scaler = self.amp_scaler
+            scaler.scale(sum(losses.values())).backward()
+            scaler.unscale_(opt)      # in place on the bucket views; clipping itself happens inside opt.step()
+            if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+                # DDP's all-reduce would spread an inf/nan to every rank; the sharded step must agree on
+                # skipping before anybody enters the reduce-scatter
+                for found in scaler._per_optimizer_states[id(opt)]["found_inf_per_device"].values():
+                    dist.all_reduce(found, op=dist.ReduceOp.MAX)
+            scaler.step(opt)
+            scaler.update()
         else:
             opt.zero_grad()
             preds, losses = self.distiller(image=image, target=target, epoch=epoch)

@@ -96,6 +96,6 @@ def test_reference_base_trainer_gets_flat_sgd(patched):
     tr = E.trainer_dict["base"]("exp3", distiller, [], [], cfg)
     assert isinstance(tr.optimizer, b200.FlatAdam) and tr.optimizer.decoupled and tr.optimizer.max_grad_norm == 1.0
     assert tr.optimizer.param_groups[0]["betas"] == tuple(cfg.SOLVER.ADAM.BETAS)
-    cfg.EXPERIMENT.AMP = True
+    cfg.EXPERIMENT.AMP, cfg.SOLVER.TRAINER = True, "dot"          # DOT refuses AMP, as the reference (trainer.py:377-378)
     with pytest.raises(NotImplementedError):
-        E.trainer_dict["base"]("exp4", distiller, [], [], cfg)
+        E.trainer_dict["dot"]("exp4", distiller, [], [], cfg)
