@@ -50,7 +50,7 @@ def parse():
     ap.add_argument("--comm", default="auto",
                     choices=["auto", "nccl", "fused", "fused_kd", "fused_p2p", "fused_kd_p2p"],
                     help="data-parallel step (N > 1): NCCL launches or the fused NVLink kernel; auto = fused "
-                         "(peer access at N <= 2, NVSwitch multicast with both buckets in the kernel above), "
+                         "(peer access at N <= 4, NVSwitch multicast with both buckets in the kernel above), "
                          "NCCL launches if symmetric memory cannot be set up")
     ap.add_argument("--no-sweep", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
@@ -315,7 +315,9 @@ def run_b200_arm(args):
     distiller = b200.distiller_dict[cfg.DISTILLER.TYPE](student, teacher, cfg).to(dev).train()
     comm_mode = args.comm
     if comm_mode == "auto":
-        comm_mode = "nccl" if world == 1 else ("fused_p2p" if world <= 2 else "fused_kd")
+        # measured on one HGX box (profiles/r1_bench_n*): peer loads win up to 4 GPUs, the in-switch
+        # (NVLS multicast) reduction of both buckets wins at 8
+        comm_mode = "nccl" if world == 1 else ("fused_p2p" if world <= 4 else "fused_kd")
     comm_note = ""
     b200.TailStepMixin.comm_mode = comm_mode
     try:

@@ -73,6 +73,7 @@ def _opt_worker(rank, world, port, case_idx, out, mode="nccl"):
     (2, 0, "nccl"), (2, 2, "nccl"), (4, 6, "nccl"), (8, 6, "nccl"),
     # one fused kernel over NVLink symmetric memory: NVLS multicast, both buckets in-switch, plain peer access
     (2, 0, "fused"), (2, 6, "fused_kd"), (2, 6, "fused_p2p"), (2, 2, "fused"),
+    (4, 6, "fused_kd"), (4, 0, "fused_p2p"),
     (8, 6, "fused"), (8, 6, "fused_kd"), (8, 6, "fused_kd_p2p"),
 ])
 def test_sharded_dot_step_matches_oracle_on_rank_averaged_gradients(world, case_idx, mode, tmp_path):
