@@ -394,16 +394,23 @@ def run_b200_arm(args):
     clocks = sampler.summary(t_wall0, t_wall1)
 
     # end-to-end: public call with host (pinned) batch, H2D + metrics D2H inside the timed region
+    # (metrics_lag = 1: the loss/top-k read-back of step i is awaited during step i+1, which lets the
+    #  H2D copy of the next batch overlap the current step; every step's result is still read inside
+    #  the timed region, the last one by flush_metrics)
     meters = b200.new_train_meters()
+    trainer.metrics_lag = 1
     for _ in range(2):
         trainer.train_iter(host, epoch, meters)
+    trainer.flush_metrics(meters)
     barrier()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
     for _ in range(args.steps):
         trainer.train_iter(host, epoch, meters)
+    trainer.flush_metrics(meters)
     f1.record()
     barrier()
+    assert meters["top1"].count == (2 + args.steps) * per_gpu * world, "a step's metrics were not read back"
     sampler.stop()
     e2e_secs = f0.elapsed_time(f1) * 1e-3
 
@@ -466,7 +473,7 @@ def run_b200_arm(args):
         "e2e": {"value": world * per_gpu * args.steps / e2e_secs, "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 20, "ms_per_step": 1e3 * e2e_secs / args.steps,
                 "api": "StandaloneTrainer.train_iter((image, target, index), epoch, meters) -- the mirror of "
-                       "DOT.train_iter (trainer.py:412-461)"},
+                       "DOT.train_iter (trainer.py:412-461); metrics_lag=1, flushed inside the timed region"},
         "gpu_launches": launches,
         "optimizer_step": {"us": 1e6 * sum(step_t) / max(1, len(step_t)),
                            "what": "optimizer.step(): task-bucket collective + DOT kernel + parameter write-back, "

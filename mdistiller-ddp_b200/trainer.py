@@ -103,12 +103,27 @@ class TailStepMixin:
         return opt
 
     # ---------------------------------------------------------------- one iteration
+    # metrics_lag = 0: the progress line of an iteration contains that iteration (the reference's
+    # behaviour, one host sync per step).  metrics_lag = k > 0: the device-to-host read of step i is
+    # only waited for at step i+k, so the host can already enqueue the next batch's H2D copy and
+    # kernels while the GPU finishes step i; call flush_metrics() before reading the meters.
+    metrics_lag = 0
+
     def train_iter(self, data, epoch, train_meters):
         t0 = time.time()
         image, target, index = data
         train_meters["data_time"].update(time.time() - t0)
-        image = image.float().cuda(non_blocking=True)
-        target = target.cuda(non_blocking=True)
+        # H2D on a side stream: with lagged metrics the copy of batch i+1 overlaps the kernels of step i
+        copy_stream = self.__dict__.get("_copy_stream")
+        if copy_stream is None:
+            copy_stream = self._copy_stream = torch.cuda.Stream()
+        main = torch.cuda.current_stream()
+        with torch.cuda.stream(copy_stream):
+            image = image.float().cuda(non_blocking=True)
+            target = target.cuda(non_blocking=True)
+        main.wait_stream(copy_stream)
+        image.record_stream(main)
+        target.record_stream(main)
         preds, losses = self.tail_step(image, target, epoch)
         train_meters["training_time"].update(time.time() - t0)
         return self.report(preds, target, losses, epoch, train_meters)
@@ -171,23 +186,48 @@ class TailStepMixin:
         k = min(5, preds.shape[1])
         top = preds.topk(k, dim=1).indices
         hit = top.eq(target.view(-1, 1))
+        # (torch.full launches a fill kernel; torch.tensor(x, device=...) would be a blocking pageable H2D copy
+        #  that stalls the host until the whole step has drained)
         pack = torch.stack([losses["loss_ce"].detach().float(), losses["loss_kd"].detach().float(),
                             hit[:, 0].sum().float(), hit.sum().float(),
-                            torch.tensor(float(batch), device=preds.device)])
+                            torch.full((), float(batch), device=preds.device)])
         world = 1
         if dist.is_available() and dist.is_initialized():
             dist.all_reduce(pack)
             world = dist.get_world_size()
-        ce, kd, c1, c5, n = pack.cpu().tolist()
+        pending = self.__dict__.setdefault("_pending_metrics", [])
+        host = torch.empty(5, dtype=torch.float32, pin_memory=True)
+        host.copy_(pack, non_blocking=True)
+        done = torch.cuda.Event()
+        done.record()
+        pending.append((done, host, world))
+        while len(pending) > self.metrics_lag:
+            self._consume_metrics(pending.pop(0), train_meters)
+        return self._progress_line(epoch, train_meters)
+
+    def _consume_metrics(self, entry, train_meters) -> None:
+        done, host, world = entry
+        done.synchronize()
+        ce, kd, c1, c5, n = host.tolist()
         vals = {"loss_ce": ce / world, "loss_kd": kd / world, "_total": (ce + kd) / world}
         n = int(n)
         for name, v in vals.items():
             train_meters["losses"].setdefault(name, _Meter()).update(v, n)
         train_meters["top1"].update(100.0 * c1 / n, n)
         train_meters["top5"].update(100.0 * c5 / n, n)
+
+    def flush_metrics(self, train_meters) -> None:
+        """Wait for and account every outstanding iteration (needed only with metrics_lag > 0)."""
+        pending = self.__dict__.get("_pending_metrics", [])
+        while pending:
+            self._consume_metrics(pending.pop(0), train_meters)
+
+    @staticmethod
+    def _progress_line(epoch, train_meters) -> str:
+        total = train_meters["losses"]["_total"].avg if "_total" in train_meters["losses"] else float("nan")
         return "Epoch:{}| Time(data):{:.3f}| Time(train):{:.3f}| Loss:{:.4f}| Top-1:{:.3f}| Top-5:{:.3f}".format(
-            epoch, train_meters["data_time"].avg, train_meters["training_time"].avg,
-            train_meters["losses"]["_total"].avg, train_meters["top1"].avg, train_meters["top5"].avg)
+            epoch, train_meters["data_time"].avg, train_meters["training_time"].avg, total,
+            train_meters["top1"].avg, train_meters["top5"].avg)
 
 
 class StandaloneTrainer(TailStepMixin):

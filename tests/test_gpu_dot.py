@@ -320,3 +320,27 @@ def test_base_trainer_amp_branch(b200):
     amp_tr.tail_step(image.cuda(), target.cuda(), 10)
     assert torch.equal(amp_tr.optimizer.flat_params, after)
     assert amp_tr.amp_scaler.get_scale() == 2.0 ** 119
+
+
+def test_lagged_metrics_account_every_iteration(b200):
+    """metrics_lag > 0 defers the device-to-host read; after flush_metrics the meters equal the eager ones."""
+    from mdistiller_ddp_b200 import workloads as W
+    import copy
+    torch.manual_seed(5)
+    teacher, student = W.TinyNet(100, 24), W.TinyNet(100, 16)
+    t2, s2 = copy.deepcopy(teacher), copy.deepcopy(student)
+    cfg = W.default_cfg("cifar_res32x4_res8x4_kd_dot")
+    eager = b200.StandaloneTrainer(b200.KD(student, teacher, cfg).cuda().train(), cfg)
+    lagged = b200.StandaloneTrainer(b200.KD(s2, t2, cfg).cuda().train(), cfg)
+    lagged.metrics_lag = 2
+    m1, m2 = b200.new_train_meters(), b200.new_train_meters()
+    for step in range(5):
+        batch = W.synthetic_batch(16, 32, 100, seed=60 + step, pin=True)
+        eager.train_iter(batch, 1, m1)
+        lagged.train_iter(batch, 1, m2)
+        assert m1["top1"].count == 16 * (step + 1) and m2["top1"].count == 16 * max(0, step - 1)
+    lagged.flush_metrics(m2)
+    assert m2["top1"].count == m1["top1"].count == 80
+    for k in ("loss_ce", "loss_kd", "_total"):
+        assert abs(m1["losses"][k].avg - m2["losses"][k].avg) <= 1e-5 * abs(m1["losses"][k].avg)
+    assert m1["top5"].avg == m2["top5"].avg
