@@ -54,6 +54,10 @@ class _FlatOptimizer(Optimizer):
             self._buckets[name] = b
             self._views[name] = self._space.views(b)
         self._phase = self._bucket_names[0]
+        # set by a trainer that only ever lets autograd write the gradients: skips the per-parameter
+        # "did the caller assign a tensor of its own?" check in step()/step_kd()
+        self.trust_bucket_grads = False
+        self._all_true = [True] * len(plist)
         self._touched = set()
         self._index = {id(p): i for i, p in enumerate(plist)}
         self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in plist if p.requires_grad]
@@ -77,6 +81,11 @@ class _FlatOptimizer(Optimizer):
 
     def _collect(self, name: str) -> List[bool]:
         """Which parameters have a gradient for this pass; foreign tensors are copied in."""
+        if self.trust_bucket_grads:          # caller guarantees p.grad are still our views (our own trainers do)
+            touched = self._touched
+            if len(touched) == len(self._space.params):
+                return self._all_true
+            return [i in touched for i in range(len(self._space.params))]
         views = self._views[name]
         has = []
         for i, (p, v) in enumerate(zip(self._space.params, views)):
@@ -200,6 +209,7 @@ class DistillationOrientedTrainer(_FlatOptimizer):
         self._kd_members: Optional[List[bool]] = None
         self._kd_work = None
         self._kd_prereduced = True
+        self._steady, self._steady_runs = False, None
         self.last_fused = None          # set by every fused step: {"multicast": bool, "kd_in_kernel": bool}
 
     @torch.no_grad()
@@ -228,13 +238,17 @@ class DistillationOrientedTrainer(_FlatOptimizer):
         group = self.param_groups[0]
         task_members = self._collect("task")
         kd_members = self._kd_members if self._kd_members is not None else [False] * len(task_members)
-        modes = []
-        for i, (t, k) in enumerate(zip(task_members, kd_members)):
-            m = (_BOTH if k else _TASK) if t else (_KD if k else _NONE)
-            modes.append((m, t and not self._has_vt[i], k and not self._has_vk[i]))
         sp = self._space
         momentum = group["momentum"]
-        runs = self._runs(modes)
+        steady = (self._steady and task_members is self._all_true and kd_members is self._all_true)
+        if steady:      # every parameter in both lists and every buffer already exists: one cached run
+            runs = self._steady_runs
+        else:
+            modes = []
+            for i, (t, k) in enumerate(zip(task_members, kd_members)):
+                m = (_BOTH if k else _TASK) if t else (_KD if k else _NONE)
+                modes.append((m, t and not self._has_vt[i], k and not self._has_vk[i]))
+            runs = self._runs(modes)
         hp = dict(lr=group["lr"], momentum=momentum, momentum_kd=group["momentum_kd"],
                   weight_decay=group["weight_decay"], dampening=group["dampening"],
                   grad_scale=1.0 / self._comm.world_size)
@@ -262,11 +276,15 @@ class DistillationOrientedTrainer(_FlatOptimizer):
                     first_task=first_t, first_kd=first_k, membership=_MEMBERSHIP[m], **hp)
             self._comm.all_gather(sp.flat)
 
-        for i, (t, k) in enumerate(zip(task_members, kd_members)):
-            if t and momentum != 0:
-                self._has_vt[i] = True
-            if k:
-                self._has_vk[i] = True
+        if not steady:
+            for i, (t, k) in enumerate(zip(task_members, kd_members)):
+                if t and momentum != 0:
+                    self._has_vt[i] = True
+                if k:
+                    self._has_vk[i] = True
+            if all(self._has_vk) and (momentum == 0 or all(self._has_vt)):
+                self._steady = True
+                self._steady_runs = self._runs([(_BOTH, False, False)] * len(self._has_vk))
         self._kd_members = None
         self._phase = "kd"
         return loss
@@ -305,6 +323,7 @@ class DistillationOrientedTrainer(_FlatOptimizer):
         self._import_state((("momentum_buffer", self._v_task, self._has_vt),
                             ("momentum_kd_buffer", self._v_kd, self._has_vk)))
         self._run_cache.clear()
+        self._steady = False
 
     def momentum_views(self):
         """Per-parameter views of the (unsharded) momentum buffers -- single-process use."""

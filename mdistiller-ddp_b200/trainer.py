@@ -79,11 +79,11 @@ class TailStepMixin:
                 raise NotImplementedError("AMP is not supported for DOT.")
             if cfg.SOLVER.TYPE != "SGD":
                 raise NotImplementedError(cfg.SOLVER.TYPE)
-            return DistillationOrientedTrainer(
+            return _trust(DistillationOrientedTrainer(
                 params, lr=cfg.SOLVER.LR,
                 momentum=cfg.SOLVER.SGD.MOMENTUM - cfg.SOLVER.DOT.DELTA,
                 momentum_kd=cfg.SOLVER.SGD.MOMENTUM + cfg.SOLVER.DOT.DELTA,
-                weight_decay=cfg.SOLVER.WEIGHT_DECAY, comm=comm)
+                weight_decay=cfg.SOLVER.WEIGHT_DECAY, comm=comm))
         # AMP (trainer.py:79-80, 268, 304-313): autocast forward + torch's GradScaler around our step; the
         # scaled loss then has to go through autograd, so the pre-combined gradient shortcut is off
         self.use_amp = bool(cfg.EXPERIMENT.AMP)
@@ -100,7 +100,7 @@ class TailStepMixin:
         else:
             raise NotImplementedError(kind)
         opt.max_grad_norm = float(getattr(cfg.SOLVER, "GRAD_CLIP", 0.0) or 0.0)   # clip inside step(), on the shard
-        return opt
+        return _trust(opt)
 
     # ---------------------------------------------------------------- one iteration
     # metrics_lag = 0: the progress line of an iteration contains that iteration (the reference's
@@ -228,6 +228,11 @@ class TailStepMixin:
         return "Epoch:{}| Time(data):{:.3f}| Time(train):{:.3f}| Loss:{:.4f}| Top-1:{:.3f}| Top-5:{:.3f}".format(
             epoch, train_meters["data_time"].avg, train_meters["training_time"].avg, total,
             train_meters["top1"].avg, train_meters["top5"].avg)
+
+
+def _trust(opt):
+    opt.trust_bucket_grads = True     # tail_step never assigns p.grad itself: autograd writes into the buckets
+    return opt
 
 
 class StandaloneTrainer(TailStepMixin):
