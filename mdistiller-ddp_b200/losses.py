@@ -65,6 +65,7 @@ class _DistillTail(torch.autograd.Function):
             temperature=float(temperature), kd_scale=float(kd_scale), ce_mode=ops.CE_SPLIT,
             ce_scale=float(ce_scale))
         ctx.save_for_backward(grad_kd, grad_ce)
+        ctx.set_materialize_grads(False)      # a loss that takes no part in a backward arrives as None, not zeros
         stash.extend((loss_pair, grad_kd, grad_ce))
         return loss_pair[0], loss_pair[1]
 

@@ -192,3 +192,25 @@ def test_autograd_functions_match_reference_signatures(ops, loss_golden):
     (l_kd + l_ce).backward()
     want = loss_golden[f"{case.name}/gdkd64"] + loss_golden[f"{case.name}/gce64"]
     assert oracle.max_rel_err(a.grad, want) <= TOL
+
+
+def test_rejected_inputs_raise(ops):
+    """Argument problems surface as Python exceptions, like the reference."""
+    z = torch.zeros(4, 8, device="cuda")
+    y = torch.zeros(4, dtype=torch.long, device="cuda")
+    with pytest.raises(RuntimeError, match="invalid argument"):
+        ops.distill_loss(z[:0], z[:0], y[:0], kind=ops.LOSS_DKD)                    # no rows
+    with pytest.raises(RuntimeError, match="invalid argument"):
+        ops.distill_loss(z, z, y, kind=ops.LOSS_DKD, temperature=0.0)
+    with pytest.raises(RuntimeError, match="invalid argument"):
+        ops.distill_loss(z[:, :1].contiguous(), z[:, :1].contiguous(), y, kind=ops.LOSS_DKD)   # DKD needs >= 2 classes
+    with pytest.raises(ValueError):
+        ops.distill_loss(z, z[:, :4], y, kind=ops.LOSS_KD)
+    with pytest.raises(TypeError):
+        ops.distill_loss(z, z, y.int(), kind=ops.LOSS_DKD)
+    with pytest.raises(TypeError):
+        ops.distill_loss(z.double(), z.double(), y, kind=ops.LOSS_DKD)
+    # labels outside [0, classes) touch no memory: the row simply has no label column
+    bad = torch.tensor([0, 99, -3, 7], device="cuda")
+    lp, g, _ = ops.distill_loss(torch.randn(4, 8, device="cuda"), torch.randn(4, 8, device="cuda"), bad, kind=ops.LOSS_DKD)
+    assert torch.isfinite(g).all()
