@@ -193,6 +193,23 @@ MDB200_API int mdb200_dot_step_fused(float *p_local, float *p_multicast, float *
                     float dampening, float grad_scale, int first_task, int first_kd, void *stream);
 
 /*
+ * Multi-tensor gather: copy n_tensors per-parameter gradient tensors into one flat fp32 bucket in a
+ * single launch (zero-filling the slices of parameters that have no gradient, src_ptrs[i] == NULL).
+ *
+ * Replaces the reference's reliance on `zero_grad(set_to_none=True)` + captured `p.grad` tensors
+ * (mdistiller/engine/dot.py:111-123, trainer.py:427-431) and DDP's gradient-to-bucket copies
+ * (tools/train.py:86) on the way into the flat step / reduce-scatter.
+ *
+ *   src_ptrs         host array[n_tensors] of device pointers (contiguous fp32 tensors) or NULL
+ *   chunk_table_dev  device array[n_chunks][4] of int64 {tensor index, element count, source element
+ *                    offset, bucket element offset}; shape-dependent only, built once by the caller;
+ *                    chunks of one tensor must tile it exactly
+ * 8 algorithmic bytes per gathered element.
+ */
+MDB200_API int mdb200_gather_flat(float *dst_flat, const float *const *src_ptrs, int n_tensors,
+                    const int64_t *chunk_table_dev, int64_t n_chunks, void *stream);
+
+/*
  * Single-momentum SGD on a flat range, in place: torch.optim.SGD(momentum,
  * weight_decay, dampening, nesterov=False) as built by BaseTrainer.init_optimizer
  * (mdistiller/engine/trainer.py:86-91) and stepped at trainer.py:321.

@@ -76,6 +76,16 @@ class FlatSpace:
     def views(self, buf: torch.Tensor) -> List[torch.Tensor]:
         return [buf[o:o + p.numel()].view(p.shape) for o, p in zip(self.offsets, self.params)]
 
+    def chunk_table(self, chunk_elems: int = 16384) -> torch.Tensor:
+        """int64 [n_chunks, 4] = {tensor index, count, source offset, bucket offset}: how
+        `mdb200_gather_flat` tiles the per-parameter gradients into a bucket (64 KB per thread block)."""
+        rows = []
+        for i, (o, p) in enumerate(zip(self.offsets, self.params)):
+            n = p.numel()
+            for s in range(0, n, chunk_elems):
+                rows.append((i, min(chunk_elems, n - s), s, o + s))
+        return torch.tensor(rows, dtype=torch.int64, device=self.device).reshape(-1, 4).contiguous()
+
     def shard(self, buf: torch.Tensor) -> torch.Tensor:
         return buf[self.shard_lo:self.shard_hi]
 

@@ -202,6 +202,24 @@ def clip_coefficient(total_sumsq: torch.Tensor, max_norm: float, out: Optional[t
     return out
 
 
+def gather_flat(dst_flat: torch.Tensor, src_ptrs, chunk_table: torch.Tensor) -> None:
+    """One launch: scatter-free copy of per-parameter gradient tensors (device addresses, 0 = none)
+    into the flat bucket; see mdb200_gather_flat."""
+    global launch_count
+    import ctypes as C
+    lib = _lib.load()
+    _need_cuda_f32(dst_flat, "dst_flat")
+    if not chunk_table.is_cuda or chunk_table.dtype != torch.int64 or not chunk_table.is_contiguous():
+        raise TypeError("chunk_table must be a contiguous CUDA int64 tensor")
+    n = len(src_ptrs)
+    table = (C.c_void_p * n)(*src_ptrs)
+    with torch.cuda.device(dst_flat.device):
+        rc = lib.mdb200_gather_flat(dst_flat.data_ptr(), table, n, chunk_table.data_ptr(), chunk_table.shape[0],
+                                    _stream_ptr(dst_flat.device))
+    _lib.check(rc, "mdb200_gather_flat")
+    launch_count += 1
+
+
 def dot_step_fused(p_local: torch.Tensor, g_task_local: torch.Tensor, g_kd_local: torch.Tensor,
                    v_task: Optional[torch.Tensor], v_kd: torch.Tensor, *, multicast=None, peers=None,
                    kd_is_reduced: bool, shard_lo: int, shard_len: int, world: int, lr: float, momentum: float,

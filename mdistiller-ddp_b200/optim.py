@@ -57,6 +57,11 @@ class _FlatOptimizer(Optimizer):
         # set by a trainer that only ever lets autograd write the gradients: skips the per-parameter
         # "did the caller assign a tensor of its own?" check in step()/step_kd()
         self.trust_bucket_grads = False
+        # gather mode (CUDA, trusted callers): zero_grad() sets p.grad = None, autograd hands over its own
+        # gradient tensors, and ONE multi-tensor launch copies them into the bucket -- instead of one add_
+        # launch per parameter per backward when autograd accumulates into bucket views
+        self.gather_grads = False
+        self._chunk_table = None
         self._all_true = [True] * len(plist)
         self._touched = set()
         self._index = {id(p): i for i, p in enumerate(plist)}
@@ -67,8 +72,19 @@ class _FlatOptimizer(Optimizer):
     def _on_grad(self, p: torch.Tensor) -> None:
         self._touched.add(self._index[id(p)])
 
+    def enable_gather(self) -> None:
+        for h in self._hooks:
+            h.remove()
+        self._hooks = []
+        self._chunk_table = self._space.chunk_table()
+        self.trust_bucket_grads = self.gather_grads = True
+
     def _arm(self, name: str) -> None:
         """Zero bucket `name` and make it the accumulation target of the next backward."""
+        if self.gather_grads:
+            for p in self._space.params:
+                p.grad = None          # nothing to zero: the gather overwrites (or zero-fills) every slice
+            return
         self._buckets[name].zero_()
         for p, v in zip(self._space.params, self._views[name]):
             p.grad = v
@@ -81,6 +97,8 @@ class _FlatOptimizer(Optimizer):
 
     def _collect(self, name: str) -> List[bool]:
         """Which parameters have a gradient for this pass; foreign tensors are copied in."""
+        if self.gather_grads:
+            return self._gather(name)
         if self.trust_bucket_grads:          # caller guarantees p.grad are still our views (our own trainers do)
             touched = self._touched
             if len(touched) == len(self._space.params):
@@ -98,6 +116,27 @@ class _FlatOptimizer(Optimizer):
                 v.copy_(g)
                 has.append(True)
         return has
+
+    def _gather(self, name: str) -> List[bool]:
+        """Multi-tensor gather of whatever autograd left in p.grad into bucket `name`."""
+        ptrs, has, odd = [], [], []
+        dev = self._space.device
+        for i, p in enumerate(self._space.params):
+            g = p.grad
+            if g is None:
+                ptrs.append(0)
+                has.append(False)
+            elif g.is_contiguous() and g.dtype == torch.float32 and g.device == dev:
+                ptrs.append(g.data_ptr())
+                has.append(True)
+            else:                          # strided / other dtype: zero-filled by the kernel, then copied
+                ptrs.append(0)
+                has.append(True)
+                odd.append(i)
+        self._k.gather_flat(self._buckets[name], ptrs, self._chunk_table)
+        for i in odd:
+            self._views[name][i].copy_(self._space.params[i].grad)
+        return self._all_true if all(has) else has
 
     # -- runs of tensors sharing one update rule --------------------------------------
     def _runs(self, modes: Sequence[tuple]) -> list:

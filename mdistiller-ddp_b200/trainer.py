@@ -231,7 +231,12 @@ class TailStepMixin:
 
 
 def _trust(opt):
-    opt.trust_bucket_grads = True     # tail_step never assigns p.grad itself: autograd writes into the buckets
+    """tail_step owns the gradient protocol: on CUDA let autograd keep its own gradient tensors and gather
+    them into the bucket with one launch; elsewhere (CPU test doubles) trust the bucket views."""
+    if opt.flat_params.is_cuda and os.environ.get("MDB200_NO_GATHER") != "1":
+        opt.enable_gather()
+    else:
+        opt.trust_bucket_grads = True
     return opt
 
 

@@ -344,3 +344,46 @@ def test_lagged_metrics_account_every_iteration(b200):
     for k in ("loss_ce", "loss_kd", "_total"):
         assert abs(m1["losses"][k].avg - m2["losses"][k].avg) <= 1e-5 * abs(m1["losses"][k].avg)
     assert m1["top5"].avg == m2["top5"].avg
+
+
+def test_multi_tensor_gather_matches_copies(b200):
+    """mdb200_gather_flat: ragged tensor sizes, a missing gradient (zero-filled slice), padding untouched."""
+    from mdistiller_ddp_b200.flat import FlatSpace
+    torch.manual_seed(6)
+    shapes = [(64, 3, 7, 7), (64,), (5,), (1000, 512), (3, 3), (1,), (40000,)]
+    params = [torch.nn.Parameter(torch.randn(*s, device="cuda")) for s in shapes]
+    sp = FlatSpace(params)
+    table = sp.chunk_table()
+    assert table.shape[1] == 4 and int(table[:, 1].sum()) == sum(p.numel() for p in params)
+    bucket = torch.full((sp.total,), 7.0, device="cuda")
+    for o, e, p in zip(sp.offsets, sp.ends, params):            # padding slots start (and must stay) zero
+        bucket[o + p.numel():e] = 0.0
+    grads = [torch.randn_like(p) for p in params]
+    grads[2] = None
+    b200.ops.gather_flat(bucket, [0 if g is None else g.data_ptr() for g in grads], table)
+    for g, v, p in zip(grads, sp.views(bucket), params):
+        assert torch.equal(v, torch.zeros_like(p) if g is None else g)
+    for o, e, p in zip(sp.offsets, sp.ends, params):
+        assert bucket[o + p.numel():e].abs().sum().item() == 0.0
+
+
+def test_gather_mode_equals_bucket_view_mode(b200, monkeypatch):
+    """The trainer's gather protocol (p.grad = None, one gather launch per backward) and the
+    accumulate-into-bucket-views protocol give the same parameters."""
+    from mdistiller_ddp_b200 import workloads as W
+    import copy
+    torch.manual_seed(7)
+    teacher, student = W.TinyNet(100, 24), W.TinyNet(100, 16)
+    t2, s2 = copy.deepcopy(teacher), copy.deepcopy(student)
+    cfg = W.default_cfg("cifar_res32x4_res8x4_kd_dot")
+    gather = b200.StandaloneTrainer(b200.DKD(student, teacher, cfg).cuda().train(), cfg, kind="dot")
+    assert gather.optimizer.gather_grads
+    monkeypatch.setenv("MDB200_NO_GATHER", "1")
+    views = b200.StandaloneTrainer(b200.DKD(s2, t2, cfg).cuda().train(), cfg, kind="dot")
+    assert not views.optimizer.gather_grads and views.optimizer.trust_bucket_grads
+    for step in range(3):
+        image, target, _ = W.synthetic_batch(16, 32, 100, seed=70 + step)
+        gather.tail_step(image.cuda(), target.cuda(), 3)
+        views.tail_step(image.cuda(), target.cuda(), 3)
+    for p, q in zip(student.parameters(), s2.parameters()):
+        assert oracle.max_rel_err(p, q) <= 1e-6
