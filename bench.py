@@ -120,7 +120,7 @@ def cpu_arm(workload: str, batch: int, steps: int, warmup: int):
         step()
     dt = time.perf_counter() - t0
     return {"value": batch * steps / dt, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{steps} steps x {batch} images of {workload} (same nets, 224x224 fp32) on the host CPU, "
+            "sample": f"{steps} steps x {batch} images of {workload} (same nets, {hw}x{hw} fp32) on the host CPU, "
                       f"torch {torch.__version__} intra-op threads={cores}",
             "ms_per_step": 1e3 * dt / steps}
 
