@@ -38,6 +38,17 @@ UNIT = "images/s"
 FALLBACK_HBM_GBS = 6650.0
 
 
+def workload_label(name: str) -> str:
+    """The same `config.workload` string in both arms (ours and --impl reference)."""
+    labels = {
+        "imagenet_r34_r18_dkd_dot": "DKD+DOT ResNet34->ResNet18, synthetic ImageNet 224x224x3, 1000 classes, random-init",
+        "imagenet_r34_r18_kd_dot": "KD+DOT ResNet34->ResNet18, synthetic ImageNet 224x224x3, 1000 classes, random-init",
+        "cifar_res32x4_res8x4_kd_dot": "KD+DOT ResNet32x4->ResNet8x4, synthetic CIFAR-100 32x32x3, 100 classes, random-init",
+        "cifar_res32x4_res8x4_dkd_base": "DKD (base trainer, SGD) ResNet32x4->ResNet8x4, synthetic CIFAR-100 32x32x3, random-init",
+    }
+    return f"{name}: {labels.get(name, name)}"
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -135,7 +146,8 @@ def run_reference_arm(args):
         "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": steps, "warmup": warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "per_step_images": args.cpu_batch, "device": "host CPU"},
+        "config": {"workload": workload_label(args.workload), "per_step_images": args.cpu_batch,
+                   "device": "host CPU (oracle port of the reference path: same nets, per-tensor DOT loop)"},
         "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -463,8 +475,7 @@ def run_b200_arm(args):
         "metric": METRIC, "value": world * per_gpu * args.steps / secs, "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * secs / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.workload}: DKD+DOT ResNet34->ResNet18, synthetic ImageNet 224x224x3, "
-                               f"1000 classes, random-init" if args.workload == "imagenet_r34_r18_dkd_dot" else args.workload,
+        "config": {"workload": workload_label(args.workload),
                    "per_gpu_batch": per_gpu, "global_batch": per_gpu * world, "student_params": n_params,
                    "parallelism": (f"dp{world}: reduce-scatter x2 -> DOT on 1/{world} shard -> all-gather (NCCL)" if args.comm == "nccl" or world == 1
                                    else f"dp{world}: fused NVLink kernel ({args.comm}): gradient sum over ranks -> DOT on 1/{world} shard -> parameters to every rank") + comm_note,
