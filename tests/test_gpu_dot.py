@@ -387,3 +387,44 @@ def test_gather_mode_equals_bucket_view_mode(b200, monkeypatch):
         views.tail_step(image.cuda(), target.cuda(), 3)
     for p, q in zip(student.parameters(), s2.parameters()):
         assert oracle.max_rel_err(p, q) <= 1e-6
+
+
+def test_tail_kernels_replay_from_a_cuda_graph(b200):
+    """The workspace-taking entry points are pure stream work (no allocation, no host sync), so the
+    loss + update pair can be captured once and replayed: same numbers as eager launches."""
+    ops = b200.ops
+    B, C, n = 256, 1000, 1_000_000
+    g = torch.Generator(device="cuda").manual_seed(8)
+    zs = torch.randn(B, C, device="cuda", generator=g) * 3
+    zt = torch.randn(B, C, device="cuda", generator=g) * 3
+    y = torch.randint(0, C, (B,), device="cuda", generator=g)
+    p0 = torch.randn(n, device="cuda", generator=g) * 0.1
+    gt, gk = torch.randn(n, device="cuda", generator=g), torch.randn(n, device="cuda", generator=g)
+    hp = dict(lr=0.05, momentum=0.825, momentum_kd=0.975, weight_decay=5e-4)
+
+    def run_eager(steps):
+        p, vt, vk = p0.clone(), torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+        for _ in range(steps):
+            lp, gkd, gce = ops.distill_loss(zs, zt, y, kind=ops.LOSS_DKD, alpha=1.0, beta=0.5, temperature=1.0,
+                                            ce_mode=ops.CE_SPLIT)
+            ops.dot_step(p, gt, gk, vt, vk, **hp)
+        return lp.clone(), gkd.clone(), p
+
+    want_l, want_g, want_p = run_eager(3)
+    p, vt, vk = p0.clone(), torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    gkd, gce, lp = torch.empty_like(zs), torch.empty_like(zs), torch.empty(2, device="cuda")
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):                       # warm-up on the capture stream (workspace, lazy init)
+        ops.distill_loss(zs, zt, y, kind=ops.LOSS_DKD, alpha=1.0, beta=0.5, temperature=1.0, ce_mode=ops.CE_SPLIT,
+                         grad_kd=gkd, grad_ce=gce, loss_out=lp)
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph, stream=side):
+        ops.distill_loss(zs, zt, y, kind=ops.LOSS_DKD, alpha=1.0, beta=0.5, temperature=1.0, ce_mode=ops.CE_SPLIT,
+                         grad_kd=gkd, grad_ce=gce, loss_out=lp)
+        ops.dot_step(p, gt, gk, vt, vk, **hp)
+    for _ in range(3):
+        graph.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(lp, want_l) and torch.equal(gkd, want_g) and torch.equal(p, want_p)
