@@ -197,3 +197,38 @@ def test_live_reference_agrees_with_oracle():
     (g,) = torch.autograd.grad(l, a)
     r = oracle.loss_and_grad("kd", zs, zt, y, temperature=case.T)
     assert torch.equal(r["loss_kd"], l.detach()) and torch.equal(r["grad_kd"], g)
+
+
+@pytest.mark.skipif(not ref_loader.available(), reason="reference tree not mounted (GPU box)")
+@pytest.mark.parametrize("kind", ["DKD", "KD"])
+def test_forward_train_composition_matches_reference_distillers(kind):
+    """a3/a5: the way the GPU tests compose the oracle (CE_WEIGHT*CE, warm-up/KD_WEIGHT * distillation
+    term) is exactly what the reference's DKD.forward_train / KD.forward_train return (DKD.py:65-84,
+    KD.py:25-39), on the same small nets."""
+    import copy
+    import sys
+    sys.path.insert(0, __import__("os").path.dirname(__file__))
+    import _ref_shims
+    _ref_shims.install_shims()
+    RefDKD, RefKD = ref_loader.distiller_classes()
+    from mdistiller_ddp_b200 import workloads as W
+    torch.manual_seed(11)
+    teacher, student = W.TinyNet(100, 24), W.TinyNet(100, 16)
+    cfg = W.default_cfg("cifar_res32x4_res8x4_kd_dot")
+    ref = (RefDKD if kind == "DKD" else RefKD)(copy.deepcopy(student), copy.deepcopy(teacher), cfg).train()
+    image, target, _ = W.synthetic_batch(16, 32, 100, seed=3)
+    for epoch in (1, 7, 40):
+        logits, losses = ref.forward_train(image=image, target=target, epoch=epoch)
+        student.train()
+        teacher.eval()
+        zs, _ = student(image)
+        with torch.no_grad():
+            zt, _ = teacher(image)
+        if kind == "DKD":
+            l_ce = cfg.DKD.CE_WEIGHT * oracle.ce_loss(zs, target)
+            l_kd = min(epoch / cfg.DKD.WARMUP, 1.0) * oracle.dkd_loss(zs, zt, target, cfg.DKD.ALPHA, cfg.DKD.BETA, cfg.DKD.T)
+        else:
+            l_ce = cfg.KD.LOSS.CE_WEIGHT * oracle.ce_loss(zs, target)
+            l_kd = cfg.KD.LOSS.KD_WEIGHT * oracle.kd_loss(zs, zt, cfg.KD.TEMPERATURE)
+        assert torch.allclose(losses["loss_ce"], l_ce, rtol=1e-6) and torch.allclose(losses["loss_kd"], l_kd, rtol=1e-6)
+        assert set(losses) == {"loss_ce", "loss_kd"} and torch.allclose(logits, zs, rtol=1e-6, atol=1e-7)
