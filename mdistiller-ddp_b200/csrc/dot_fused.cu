@@ -27,7 +27,6 @@ namespace mdb200 {
 
 constexpr int kMaxPeers = 16;
 constexpr int kFusedThreads = 256;
-constexpr int kFusedUnroll = 4;   // 4 remote 16-byte requests per gradient bucket in flight per thread
 
 struct FusedCoef {
     float neg_lr, m_task, m_kd, wd, keep, gscale;
@@ -82,7 +81,7 @@ __device__ __forceinline__ void fused_one(float &p, float gt, float gk, float &v
 }
 
 // SRC_T / SRC_K: where the task / KD gradient sums come from; MC_OUT: multicast store of P.
-template <int SRC_T, int SRC_K, bool MC_OUT>
+template <int SRC_T, int SRC_K, bool MC_OUT, int kFusedUnroll>
 __global__ void __launch_bounds__(kFusedThreads)
 dot_fused_shard(float4 *p_local, float4 *p_mc, const PeerTable p_peers,
                 const float4 *gt_src, const PeerTable gt_peers, const float4 *gk_src, const PeerTable gk_peers,
@@ -128,21 +127,31 @@ dot_fused_shard(float4 *p_local, float4 *p_mc, const PeerTable p_peers,
     }
 }
 
-template <int SRC_T, int SRC_K>
-static cudaError_t launch_fused(bool mc_out, float4 *p_local, float4 *p_mc, const PeerTable &pp, const float4 *gt,
-                                const PeerTable &gtp, const float4 *gk, const PeerTable &gkp, float4 *vt, float4 *vk,
-                                long long n4, int world, const FusedCoef &c, cudaStream_t st) {
-    const long long tile = (long long)kFusedThreads * kFusedUnroll;
+template <int SRC_T, int SRC_K, int U>
+static cudaError_t launch_fused_u(bool mc_out, float4 *p_local, float4 *p_mc, const PeerTable &pp, const float4 *gt,
+                                  const PeerTable &gtp, const float4 *gk, const PeerTable &gkp, float4 *vt, float4 *vk,
+                                  long long n4, int world, const FusedCoef &c, cudaStream_t st) {
+    const long long tile = (long long)kFusedThreads * U;
     long long blocks = (n4 + tile - 1) / tile;
     const long long cap = (long long)sm_count() * 16;
     if (blocks > cap) blocks = cap;
     if (mc_out)
-        dot_fused_shard<SRC_T, SRC_K, true><<<(unsigned)blocks, kFusedThreads, 0, st>>>(p_local, p_mc, pp, gt, gtp, gk, gkp,
-                                                                                        vt, vk, n4, world, c);
+        dot_fused_shard<SRC_T, SRC_K, true, U><<<(unsigned)blocks, kFusedThreads, 0, st>>>(p_local, p_mc, pp, gt, gtp, gk,
+                                                                                           gkp, vt, vk, n4, world, c);
     else
-        dot_fused_shard<SRC_T, SRC_K, false><<<(unsigned)blocks, kFusedThreads, 0, st>>>(p_local, p_mc, pp, gt, gtp, gk,
-                                                                                         gkp, vt, vk, n4, world, c);
+        dot_fused_shard<SRC_T, SRC_K, false, U><<<(unsigned)blocks, kFusedThreads, 0, st>>>(p_local, p_mc, pp, gt, gtp, gk,
+                                                                                            gkp, vt, vk, n4, world, c);
     return cudaGetLastError();
+}
+
+// One 16-byte slot per thread per trip measured best (N = 2, peer loads: 79 us vs 84 / 96 / 147 us for
+// 2 / 4 / 8 slots): the NVLink round trip is hidden by resident warps (~40 registers -> full occupancy),
+// not by per-thread unrolling.
+template <int SRC_T, int SRC_K>
+static cudaError_t launch_fused(bool mc_out, float4 *p_local, float4 *p_mc, const PeerTable &pp, const float4 *gt,
+                                const PeerTable &gtp, const float4 *gk, const PeerTable &gkp, float4 *vt, float4 *vk,
+                                long long n4, int world, const FusedCoef &c, cudaStream_t st) {
+    return launch_fused_u<SRC_T, SRC_K, 1>(mc_out, p_local, p_mc, pp, gt, gtp, gk, gkp, vt, vk, n4, world, c, st);
 }
 
 }  // namespace mdb200
