@@ -19,6 +19,7 @@
 // cat_mask does and what keeps (1 - pi) accurate for confident rows (Appendix A.4).
 // Everything stays finite where the reference's torch.log(0) would give inf/nan.
 
+#include <cstdlib>
 #include <mutex>
 
 #include "common.cuh"
@@ -220,7 +221,11 @@ __device__ __forceinline__ void cta_reduce_and_publish(const LossArgs &A, double
 // Register-resident kernel: a group of LPR lanes owns one row, NV float4 per lane per matrix.
 // Requires classes % 4 == 0, 16-byte aligned rows, classes <= LPR*NV*4.
 // ---------------------------------------------------------------------------------------
-template <int LPR, int NV, bool DKD, int CE, bool SPLIT>
+// STAGED: the rows of the NEXT sweep travel global -> shared memory as TMA bulk copies
+// (cp.async.bulk, completion on a per-warp mbarrier) while the warp works on the current rows in
+// registers, so every warp always has a tile in flight without a second register copy.  Needs
+// contiguous rows (ld == classes); one shared-memory tile per warp (the registers are the second buffer).
+template <int LPR, int NV, bool DKD, int CE, bool SPLIT, bool STAGED = false>
 __global__ void __launch_bounds__(kLossThreads, (NV >= 16 ? 1 : 2)) loss_rows_in_registers(const LossArgs A) {
     constexpr int GPW = 32 / LPR;  // rows per warp
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -229,30 +234,88 @@ __global__ void __launch_bounds__(kLossThreads, (NV >= 16 ? 1 : 2)) loss_rows_in
     const long long sweep = (long long)gridDim.x * kLossWarps * GPW;
     double acc_kd = 0.0, acc_ce = 0.0;
 
-    for (long long base = ((long long)blockIdx.x * kLossWarps + warp) * GPW; base < A.rows; base += sweep) {
+    extern __shared__ __align__(128) unsigned char staged_smem[];
+    unsigned long long *bar = nullptr;
+    float *tile_s = nullptr, *tile_t = nullptr;
+    unsigned parity = 0;
+    long long g_staged = -1;
+    const long long first = ((long long)blockIdx.x * kLossWarps + warp) * GPW;
+    // lane 0: start the copies of the tile whose first row is `b` (rows past the end are simply not copied)
+    auto issue_tile = [&](long long b) {
+        const long long left = A.rows - b;
+        const unsigned bytes = (unsigned)((left < GPW ? left : GPW) * A.classes * sizeof(float));
+        mbar_expect_tx(bar, 2u * bytes);
+        bulk_g2s(tile_s, A.zs + b * A.classes, bytes, bar);
+        bulk_g2s(tile_t, A.zt + b * A.classes, bytes, bar);
+    };
+    if (STAGED) {
+        const unsigned region = (unsigned)((2 * GPW * A.classes * sizeof(float) + 127) & ~127ull);
+        bar = reinterpret_cast<unsigned long long *>(staged_smem) + warp;
+        tile_s = reinterpret_cast<float *>(staged_smem + 128 + (size_t)warp * region);
+        tile_t = tile_s + (size_t)GPW * A.classes;
+        if (threadIdx.x == 0) {
+            for (int w = 0; w < kLossWarps; ++w) mbar_init(reinterpret_cast<unsigned long long *>(staged_smem) + w, 1);
+            mbar_init_fence();
+        }
+        __syncthreads();
+        if (first < A.rows) {
+            if (lane == 0) issue_tile(first);
+            if (DKD || CE != 0) g_staged = A.target[first + grp < A.rows ? first + grp : A.rows - 1];
+        }
+    }
+
+    for (long long base = first; base < A.rows; base += sweep) {
         const long long row = base + grp;
         const bool live = row < A.rows;           // idle groups of the last warp redo the last row
         const long long r = live ? row : A.rows - 1;
-        const float4 *ps = reinterpret_cast<const float4 *>(A.zs + r * A.ld_s);
-        const float4 *pt = reinterpret_cast<const float4 *>(A.zt + r * A.ld_t);
 
         float4 s[NV], t[NV];
+        long long g = -1;
+        if (STAGED) {
+            mbar_wait(bar, parity);
+            parity ^= 1u;
+            const float4 *ps = reinterpret_cast<const float4 *>(tile_s + (size_t)grp * A.classes);
+            const float4 *pt = reinterpret_cast<const float4 *>(tile_t + (size_t)grp * A.classes);
 #pragma unroll
-        for (int i = 0; i < NV; ++i) {
-            const int v = sub + i * LPR;
-            if (v < nvec) {
-                s[i] = ld_stream(ps + v);
-                t[i] = ld_stream(pt + v);
-            } else {
-                s[i] = t[i] = make_float4(kNegBig, kNegBig, kNegBig, kNegBig);
+            for (int i = 0; i < NV; ++i) {
+                const int v = sub + i * LPR;
+                if (v < nvec) {
+                    s[i] = ps[v];
+                    t[i] = pt[v];
+                } else {
+                    s[i] = t[i] = make_float4(kNegBig, kNegBig, kNegBig, kNegBig);
+                }
             }
+            g = g_staged;
+            __syncwarp();                          // every lane has its copy: the tile may be overwritten
+            const long long nb = base + sweep;
+            if (nb < A.rows) {
+                if (lane == 0) {
+                    fence_proxy_async_smem();
+                    issue_tile(nb);
+                }
+                if (DKD || CE != 0) g_staged = A.target[nb + grp < A.rows ? nb + grp : A.rows - 1];
+            }
+        } else {
+            const float4 *ps = reinterpret_cast<const float4 *>(A.zs + r * A.ld_s);
+            const float4 *pt = reinterpret_cast<const float4 *>(A.zt + r * A.ld_t);
+#pragma unroll
+            for (int i = 0; i < NV; ++i) {
+                const int v = sub + i * LPR;
+                if (v < nvec) {
+                    s[i] = ld_stream(ps + v);
+                    t[i] = ld_stream(pt + v);
+                } else {
+                    s[i] = t[i] = make_float4(kNegBig, kNegBig, kNegBig, kNegBig);
+                }
+            }
+            if (DKD || CE != 0) g = A.target[r];
         }
 
         // label logits: picked up (and, for DKD, masked out of the row) by the owning lane
         float zsg = kNegBig, ztg = kNegBig;
         int gv = -1, gc = 0;
         if (DKD || CE != 0) {
-            const long long g = A.target[r];
             const bool ok = g >= 0 && g < A.classes;
             gv = ok ? (int)(g >> 2) : -1;
             gc = (int)(g & 3);
@@ -477,9 +540,42 @@ static cudaError_t launch_regs(const LossArgs &A, int sms, cudaStream_t st) {
     return cudaGetLastError();
 }
 
+template <int LPR, int NV, bool DKD, int CE, bool SPLIT>
+static cudaError_t launch_staged(const LossArgs &A, int sms, cudaStream_t st) {
+    constexpr int GPW = 32 / LPR;
+    constexpr int rows_per_cta = kLossWarps * GPW;
+    auto kernel = loss_rows_in_registers<LPR, NV, DKD, CE, SPLIT, true>;
+    const size_t region = (2 * (size_t)GPW * A.classes * sizeof(float) + 127) & ~(size_t)127;
+    const size_t smem = 128 + kLossWarps * region;
+    static size_t configured = 0;
+    if (smem > configured) {
+        cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        configured = smem;
+    }
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kLossThreads, smem) != cudaSuccess || occ < 1) occ = 1;
+    long long want = (A.rows + rows_per_cta - 1) / rows_per_cta;
+    const long long cap = (long long)sms * occ;
+    if (want > cap) want = cap;
+    if (want > kMaxCtas) want = kMaxCtas;
+    if (want > A.slots) return kGridExceedsSlots;
+    kernel<<<(unsigned)want, kLossThreads, smem, st>>>(A);
+    return cudaGetLastError();
+}
+
 template <bool DKD, int CE, bool SPLIT>
 static cudaError_t launch_shape(const LossArgs &A, bool vec_ok, int sms, cudaStream_t st) {
     const long long nvec = A.classes >> 2;
+    // TMA-staged variants where they measured faster (B200): narrow rows at any batch (65536x100: -9 %), 1000-class
+    // rows up to mid-size batches (4096x1000: -10 %, 16384x1000: -3 %; +4.5 % at 65536x1000, so not there).
+    // MDB200_LOSS_STAGED=0 switches them off for A/B timing.
+    static const bool staged = !(getenv("MDB200_LOSS_STAGED") && atoi(getenv("MDB200_LOSS_STAGED")) == 0);
+    if (staged && vec_ok && A.ld_s == A.classes && A.ld_t == A.classes) {
+        if (nvec <= 28) return launch_staged<4, 7, DKD, CE, SPLIT>(A, sms, st);
+        if (nvec <= 32) return launch_staged<8, 4, DKD, CE, SPLIT>(A, sms, st);
+        if (nvec > 128 && nvec <= 256 && A.rows <= 32768) return launch_staged<32, 8, DKD, CE, SPLIT>(A, sms, st);
+    }
     if (vec_ok && nvec <= 28) return launch_regs<4, 7, DKD, CE, SPLIT>(A, sms, st);     // classes <= 112 (CIFAR-100: 25 of 28 slots)
     if (vec_ok && nvec <= 32) return launch_regs<8, 4, DKD, CE, SPLIT>(A, sms, st);
     if (vec_ok && nvec <= 128) return launch_regs<32, 4, DKD, CE, SPLIT>(A, sms, st);

@@ -18,4 +18,4 @@ for (B, C, T, beta, ce) in [(65536, 100, 4.0, 8.0, 0), (65536, 100, 4.0, 8.0, 1)
     gk, gc, lo = torch.empty_like(zs), torch.empty_like(zs), torch.empty(2, device=dev)
     med, best = timed(lambda: ops.distill_loss(zs, zt, y, kind=ops.LOSS_DKD, alpha=1.0, beta=beta, temperature=T, ce_mode=ce, grad_kd=gk, grad_ce=gc, loss_out=lo))
     nb = (16 if ce else 12) * B * C
-    print(f"variant={os.environ.get('MDB200_LOSS_PREFETCH','0')} {B}x{C} ce={ce}: {med:7.1f} us (best {best:6.1f})  {nb/med/1e3:7.0f} GB/s", flush=True)
+    print(f"variant={os.environ.get('MDB200_LOSS_STAGED','0')} {B}x{C} ce={ce}: {med:7.1f} us (best {best:6.1f})  {nb/med/1e3:7.0f} GB/s", flush=True)
