@@ -33,10 +33,33 @@ def dot(n):
     torch.cuda.synchronize()
 
 
+def gather(shapes):
+    from mdistiller_ddp_b200.flat import FlatSpace
+    params = [torch.nn.Parameter(torch.randn(*s, device=dev)) for s in shapes]
+    sp = FlatSpace(params)
+    table, bucket = sp.chunk_table(), torch.zeros(sp.total, device=dev)
+    grads = [torch.randn_like(p) for p in params]
+    for _ in range(reps):
+        ops.gather_flat(bucket, [g.data_ptr() for g in grads], table)
+    torch.cuda.synchronize()
+
+
+def adam(n):
+    p, g, m = (torch.randn(n, device=dev) * 0.1 for _ in range(3))
+    v = torch.rand(n, device=dev) * 1e-3
+    for _ in range(reps):
+        ops.adam_step(p, g, m, v, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=1e-4, step=10)
+    torch.cuda.synchronize()
+
+
 loss(65536, 1000, 1.0, 0.5, ops.CE_NONE)
 loss(65536, 1000, 1.0, 0.5, ops.CE_SPLIT)
 loss(65536, 100, 4.0, 8.0, ops.CE_NONE)
 loss(256, 1000, 1.0, 0.5, ops.CE_SPLIT)
+loss(16384, 1000, 1.0, 0.5, ops.CE_NONE)      # TMA-staged path
 dot(25_557_032)
 dot(11_689_512)
+adam(25_557_032)
+import torchvision.models as tvm
+gather([tuple(p.shape) for p in tvm.resnet18(weights=None).parameters()])
 print("ok")
