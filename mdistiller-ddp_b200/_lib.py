@@ -61,19 +61,20 @@ def load() -> C.CDLL:
     with _lock:
         if _lib is not None:
             return _lib
-        if not os.path.exists(LIB_PATH):
+        path = os.environ.get("MDB200_LIB", LIB_PATH)      # developer knob: A/B a differently built library
+        if not os.path.exists(path):
             raise KernelLibraryError(
-                f"{LIB_PATH} is missing: the sm_100a kernels are not built. "
+                f"{path} is missing: the sm_100a kernels are not built. "
                 "Run `python __graft_entry__.py` (needs nvcc). There is no CPU/PyTorch fallback.")
         try:
-            lib = C.CDLL(LIB_PATH)
+            lib = C.CDLL(path)
         except OSError as e:  # pragma: no cover
-            raise KernelLibraryError(f"cannot load {LIB_PATH}: {e}") from e
+            raise KernelLibraryError(f"cannot load {path}: {e}") from e
         for name, (res, args) in SIGNATURES.items():
             try:
                 fn = getattr(lib, name)
             except AttributeError as e:
-                raise KernelLibraryError(f"{LIB_PATH} does not export {name}; rebuild it") from e
+                raise KernelLibraryError(f"{path} does not export {name}; rebuild it") from e
             fn.restype, fn.argtypes = res, args
         got = lib.mdb200_abi_version()
         if got != ABI_VERSION:
