@@ -210,6 +210,19 @@ MDB200_API int mdb200_gather_flat(float *dst_flat, const float *const *src_ptrs,
                     const int64_t *chunk_table_dev, int64_t n_chunks, void *stream);
 
 /*
+ * Metrics record of one iteration in one launch: record[5] = {*loss_ce, *loss_kd, top-1 hits,
+ * top-5 hits, rows} for [rows, classes] fp32 logits and int64 labels.
+ *
+ * Replaces accuracy() (mdistiller/engine/utils.py:125-136: topk + eq + sums) and the per-scalar
+ * packing on the metrics tail of train_iter (mdistiller/engine/trainer.py:277-290, 436-450); the
+ * host code all-reduces the record once and reads it back once.  record[2] and record[3] must be
+ * zero on entry (they are accumulated); loss pointers may be NULL (recorded as 0).  Equal logits
+ * rank by class index (torch.topk leaves the order of equal values unspecified).
+ */
+MDB200_API int mdb200_metrics_record(const float *logits, const int64_t *target, int64_t rows, int64_t classes,
+                    int64_t ld, const float *loss_ce, const float *loss_kd, float *record, void *stream);
+
+/*
  * Single-momentum SGD on a flat range, in place: torch.optim.SGD(momentum,
  * weight_decay, dampening, nesterov=False) as built by BaseTrainer.init_optimizer
  * (mdistiller/engine/trainer.py:86-91) and stepped at trainer.py:321.

@@ -202,6 +202,33 @@ def clip_coefficient(total_sumsq: torch.Tensor, max_norm: float, out: Optional[t
     return out
 
 
+def metrics_record(logits: torch.Tensor, target: torch.Tensor, loss_ce: Optional[torch.Tensor],
+                   loss_kd: Optional[torch.Tensor]) -> torch.Tensor:
+    """5 floats on the device: {loss_ce, loss_kd, top-1 hits, top-5 hits, rows} -- one launch."""
+    global launch_count
+    lib = _lib.load()
+    _need_cuda_f32(logits, "logits")
+    if logits.dim() != 2 or logits.stride(1) != 1:
+        logits = logits.reshape(logits.shape[0], -1).contiguous()
+    if not target.is_cuda or target.dtype != torch.int64:
+        raise TypeError("target must be a CUDA int64 tensor")
+    target = target.reshape(-1).contiguous()
+    rec = torch.zeros(5, dtype=torch.float32, device=logits.device)
+
+    def scalar(t):
+        if t is None:
+            return None
+        _need_cuda_f32(t, "loss")
+        return t.data_ptr()
+    with torch.cuda.device(logits.device):
+        rc = lib.mdb200_metrics_record(logits.data_ptr(), target.data_ptr(), logits.shape[0], logits.shape[1],
+                                       logits.stride(0), scalar(loss_ce), scalar(loss_kd), rec.data_ptr(),
+                                       _stream_ptr(logits.device))
+    _lib.check(rc, "mdb200_metrics_record")
+    launch_count += 1
+    return rec
+
+
 def gather_flat(dst_flat: torch.Tensor, src_ptrs, chunk_table: torch.Tensor) -> None:
     """One launch: scatter-free copy of per-parameter gradient tensors (device addresses, 0 = none)
     into the flat bucket; see mdb200_gather_flat."""

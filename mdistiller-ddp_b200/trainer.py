@@ -22,6 +22,7 @@ from typing import Dict, Optional
 import torch
 import torch.distributed as dist
 
+from . import ops
 from .comm import ShardComm, SymmetricShardComm
 from .optim import DistillationOrientedTrainer, FlatAdam, FlatSGD
 
@@ -182,15 +183,7 @@ class TailStepMixin:
         """Cross-rank loss means and top-1/top-5 for the progress line (trainer.py:436-461):
         local counts are packed into one tensor, summed with ONE all-reduce and read back with
         ONE device-to-host copy (the reference does 2 all-gathers + 4 all-reduces + 4 syncs)."""
-        batch = target.shape[0]
-        k = min(5, preds.shape[1])
-        top = preds.topk(k, dim=1).indices
-        hit = top.eq(target.view(-1, 1))
-        # (torch.full launches a fill kernel; torch.tensor(x, device=...) would be a blocking pageable H2D copy
-        #  that stalls the host until the whole step has drained)
-        pack = torch.stack([losses["loss_ce"].detach().float(), losses["loss_kd"].detach().float(),
-                            hit[:, 0].sum().float(), hit.sum().float(),
-                            torch.full((), float(batch), device=preds.device)])
+        pack = self._metrics_pack(preds.detach(), target, losses["loss_ce"].detach(), losses["loss_kd"].detach())
         world = 1
         if dist.is_available() and dist.is_initialized():
             dist.all_reduce(pack)
@@ -204,6 +197,12 @@ class TailStepMixin:
         while len(pending) > self.metrics_lag:
             self._consume_metrics(pending.pop(0), train_meters)
         return self._progress_line(epoch, train_meters)
+
+    @staticmethod
+    def _metrics_pack(preds, target, loss_ce, loss_kd):
+        """{loss_ce, loss_kd, top-1 hits, top-5 hits, rows} on the device, one launch (fp16 logits of an
+        autocast forward are widened first)."""
+        return ops.metrics_record(preds.float(), target, loss_ce.float(), loss_kd.float())
 
     def _consume_metrics(self, entry, train_meters) -> None:
         done, host, world = entry

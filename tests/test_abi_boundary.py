@@ -31,7 +31,7 @@ def test_header_declares_the_expected_surface():
     assert set(_declared()) >= {"mdb200_abi_version", "mdb200_error_string", "mdb200_loss_workspace_bytes",
                                 "mdb200_distill_loss", "mdb200_scale_by_device_scalar", "mdb200_dot_step",
                                 "mdb200_sgd_step", "mdb200_dot_step_fused", "mdb200_distill_loss_static_scratch",
-                                "mdb200_adam_step", "mdb200_sum_squares", "mdb200_clip_coefficient", "mdb200_gather_flat"}
+                                "mdb200_adam_step", "mdb200_sum_squares", "mdb200_clip_coefficient", "mdb200_gather_flat", "mdb200_metrics_record"}
 
 
 def test_every_declared_symbol_is_exported_and_bound(lib):

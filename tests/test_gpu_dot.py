@@ -428,3 +428,34 @@ def test_tail_kernels_replay_from_a_cuda_graph(b200):
         graph.replay()
     torch.cuda.synchronize()
     assert torch.equal(lp, want_l) and torch.equal(gkd, want_g) and torch.equal(p, want_p)
+
+
+def test_metrics_record_matches_topk_accuracy(b200):
+    """top-1 / top-5 hit counts == the reference's accuracy() (engine/utils.py:125-136: topk + eq).  With exact
+    ties torch.topk's choice among equal values is unspecified, so there the count must lie between the
+    strict (all ties lose) and the inclusive (all ties win) count; the kernel ranks ties by class index."""
+    ops = b200.ops
+    torch.manual_seed(9)
+    l_ce, l_kd = torch.tensor(1.25, device="cuda"), torch.tensor(-0.5, device="cuda")
+    for B, C in ((64, 100), (256, 1000), (7, 5), (33, 3), (4096, 1000)):
+        z = torch.randn(B, C, device="cuda")
+        y = torch.randint(0, C, (B,), device="cuda")
+        rec = ops.metrics_record(z, y, l_ce, l_kd).cpu()
+        k = min(5, C)
+        hit = z.topk(k, dim=1).indices.eq(y.view(-1, 1))
+        assert rec[0].item() == 1.25 and rec[1].item() == -0.5 and rec[4].item() == B
+        assert rec[2].item() == hit[:, 0].sum().item() and rec[3].item() == hit.sum().item(), (B, C)
+        # ties
+        zt = z.clone()
+        zt[:, : C // 2] = zt[:, : C // 2].round()
+        zt[0] = 0.0
+        rec = ops.metrics_record(zt, y, None, None).cpu()
+        zg = zt.gather(1, y.view(-1, 1))
+        strict, incl = (zt > zg).sum(1), (zt >= zg).sum(1) - 1
+        for col, kk in ((2, 1), (3, k)):
+            lo, hi = (incl < kk).sum().item(), (strict < kk).sum().item()
+            assert lo <= rec[col].item() <= hi, (B, C, kk)
+        # the documented tie rule: rank = #greater + #equal with a lower class index
+        idx = torch.arange(C, device="cuda").view(1, -1)
+        rank = strict + ((zt == zg) & (idx < y.view(-1, 1))).sum(1)
+        assert rec[2].item() == (rank < 1).sum().item() and rec[3].item() == (rank < k).sum().item()
