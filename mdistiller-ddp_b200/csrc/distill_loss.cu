@@ -618,7 +618,7 @@ static int prepare_loss(LossArgs &A, bool &vec_ok, int &ce, bool &split, const f
                         float kd_scale, int ce_mode, float ce_scale, float *grad_kd, float *grad_ce,
                         int64_t ld_g, float *loss_out) {
     if (!z_student || !z_teacher || !grad_kd || !loss_out) return MDB200_EINVAL;
-    if (rows <= 0 || classes <= 0 || !(temperature > 0.f)) return MDB200_EINVAL;
+    if (rows <= 0 || classes <= 0 || classes > 0x7fffffffLL || !(temperature > 0.f)) return MDB200_EINVAL;
     if (kind != MDB200_LOSS_DKD && kind != MDB200_LOSS_KD) return MDB200_EINVAL;
     if (ce_mode < MDB200_CE_NONE || ce_mode > MDB200_CE_COMBINED) return MDB200_EINVAL;
     if (ce_mode == MDB200_CE_SPLIT && !grad_ce) return MDB200_EINVAL;
