@@ -89,24 +89,27 @@ def profiled_traffic(kernel: str, n_elements: int):
 
 # ------------------------------------------------------------------------------- CPU arm
 
-def cpu_arm(workload: str, batch: int, steps: int, warmup: int):
-    """The reference's per-step path restated on CPU (oracle/): backbones forward, dkd/kd + CE loss,
-    two backwards, per-tensor DOT loop -- the same sequence as DOT.train_iter (trainer.py:412-432)."""
+def cpu_arm(workload: str, batch: int, steps: int, warmup: int, device: str = "cpu"):
+    """The reference's per-step path restated with torch ops (oracle/): backbones forward, dkd/kd + CE loss,
+    two backwards, per-tensor DOT loop -- the same sequence as DOT.train_iter (trainer.py:412-432).
+    device="cpu" is the CPU baseline / --impl reference arm; a CUDA device gives the "reference's torch
+    formulation on the same GPU" comparator (never the product path)."""
     import oracle
     from mdistiller_ddp_b200 import workloads as W
 
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     teacher, student, hw, classes = W.build_pair(workload, seed=0)
-    teacher.eval()
-    student.train()
+    teacher.to(device).eval()
+    student.to(device).train()
     cfg = W.default_cfg(workload)
     params = [p for _, p in student.named_parameters()]
     m, d = cfg.SOLVER.SGD.MOMENTUM, cfg.SOLVER.DOT.DELTA
     opt = oracle.DotListOracle([p.data for p in params], lr=cfg.SOLVER.LR, momentum=m - d, momentum_kd=m + d,
                                weight_decay=cfg.SOLVER.WEIGHT_DECAY)
     kind = cfg.DISTILLER.TYPE
-    image, target, _ = W.synthetic_batch(batch, hw, classes, seed=1234)
+    image, target, _ = W.synthetic_batch(batch, hw, classes, seed=1234, device=device)
+    on_gpu = str(device) != "cpu"
 
     def step():
         zs, _ = student(image)
@@ -122,13 +125,17 @@ def cpu_arm(workload: str, batch: int, steps: int, warmup: int):
         opt.step_kd(list(g_kd))
         g_ce = torch.autograd.grad(l_ce, params)
         opt.step(list(g_ce))
-        return l_kd.item() + l_ce.item()
+        return l_kd.item() + l_ce.item()      # the reference reads its losses back every iteration too
 
     for _ in range(warmup):
         step()
+    if on_gpu:
+        torch.cuda.synchronize()
     t0 = time.perf_counter()
     for _ in range(steps):
         step()
+    if on_gpu:
+        torch.cuda.synchronize()
     dt = time.perf_counter() - t0
     return {"value": batch * steps / dt, "unit": UNIT, "cores": cores, "kind": "port",
             "sample": f"{steps} steps x {batch} images of {workload} (same nets, {hw}x{hw} fp32) on the host CPU, "
@@ -259,7 +266,7 @@ def kernel_sweep(dev):
     return out
 
 
-def torch_on_gpu_baseline(dev):
+def torch_on_gpu_baseline(dev, workload=None, batch=0):
     """What the kernels displace ON THE SAME GPU: the reference's torch
     formulation -- the oracle restatement of dkd_loss + autograd, and the per-tensor DOT loop -- run
     on CUDA tensors.  A baseline leg like cpu_baseline: never part of the product path."""
@@ -302,6 +309,13 @@ def torch_on_gpu_baseline(dev):
     t = timed(ref_dot, reps=10)
     n = sum(p.numel() for p in params)
     out["torch_dot_step_resnet18_62_tensors"] = {"us": t * 1e6, "algorithmic_GB/s": 32 * n / t / 1e9}
+    del params, opt, g1, g2
+    # the whole training step in the reference's torch formulation (same nets, same batch) on this GPU
+    if workload is not None:
+        r = cpu_arm(workload, batch, steps=10, warmup=5, device=dev)
+        out["torch_train_step"] = {"images/s": r["value"], "ms_per_step": r["ms_per_step"], "per_gpu_batch": batch,
+                                   "what": "oracle losses + autograd + per-tensor DOT loop on CUDA tensors, losses read back "
+                                           "each step (as trainer.py:439-444 does)"}
     return out
 
 
@@ -499,7 +513,7 @@ def run_b200_arm(args):
     if not args.no_sweep:
         line["kernels"] = kernel_sweep(dev)
         if world == 1:
-            line["torch_on_b200_baseline"] = torch_on_gpu_baseline(dev)
+            line["torch_on_b200_baseline"] = torch_on_gpu_baseline(dev, args.workload, per_gpu)
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = {k: v for k, v in cpu_arm(args.workload, args.cpu_batch, 8, 1).items()
                                 if k != "ms_per_step"}
