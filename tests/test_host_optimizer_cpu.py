@@ -340,3 +340,30 @@ def test_sharded_base_optimizers_with_clipping_world2(name, tmp_path):
         ref.step()
     for p, q in zip(got, params):
         assert oracle.max_rel_err(p, q) <= 2e-6
+
+
+def test_flat_space_layout_and_chunk_table_invariants():
+    """Every tensor starts on a 16-byte boundary, shards are equal and 16-byte aligned, and the gather
+    chunk table tiles every tensor exactly once into its slice of the bucket."""
+    import random
+    from mdistiller_ddp_b200.flat import FlatSpace
+    rng = random.Random(0)
+    for world in (1, 2, 4, 8):
+        shapes = [tuple(rng.randint(1, 9) for _ in range(rng.randint(1, 3))) for _ in range(rng.randint(1, 12))]
+        shapes.append((40000,))
+        params = [torch.nn.Parameter(torch.randn(*s)) for s in shapes]
+        before = [p.detach().clone() for p in params]
+        sp = FlatSpace(params, world_size=world, rank=world - 1)
+        assert sp.total % (4 * world) == 0 and sp.shard_len * world == sp.total and sp.shard_hi == sp.total
+        assert all(o % 4 == 0 for o in sp.offsets) and sp.shard_lo % 4 == 0
+        for p, b, o in zip(params, before, sp.offsets):
+            assert torch.equal(p, b) and p.data_ptr() == sp.flat[o:].data_ptr()      # values kept, storage moved
+        table = sp.chunk_table(chunk_elems=1000).tolist()
+        covered = torch.zeros(sp.total, dtype=torch.int32)
+        for t, n, src, dst in table:
+            assert 0 < n <= 1000 and dst == sp.offsets[t] + src and src + n <= params[t].numel()
+            covered[dst:dst + n] += 1
+        for o, e, p in zip(sp.offsets, sp.ends, params):
+            assert bool((covered[o:o + p.numel()] == 1).all()) and bool((covered[o + p.numel():e] == 0).all())
+        lo, hi = sp.clip_to_shard(0, sp.total)
+        assert (lo, hi) == (sp.shard_lo, sp.shard_hi)
