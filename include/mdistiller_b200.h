@@ -4,7 +4,9 @@
  * One shared library, plain C linkage, raw device pointers + sizes + an explicit
  * stream.  No entry point below allocates, frees or retains device memory: every
  * buffer, the reduction workspace included, belongs to the caller and must stay
- * alive until the work queued on `stream` has finished.  Calls return 0 on
+ * alive until the work queued on `stream` has finished (one variant,
+ * mdb200_distill_loss_static_scratch, uses a fixed array inside the library instead
+ * of a caller workspace).  Calls return 0 on
  * success, a negative MDB200_E* code for a rejected argument, or a positive
  * cudaError_t when the launch failed; nothing is thrown across the boundary.
  *
