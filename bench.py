@@ -45,6 +45,8 @@ def workload_label(name: str) -> str:
         "imagenet_r34_r18_kd_dot": "KD+DOT ResNet34->ResNet18, synthetic ImageNet 224x224x3, 1000 classes, random-init",
         "cifar_res32x4_res8x4_kd_dot": "KD+DOT ResNet32x4->ResNet8x4, synthetic CIFAR-100 32x32x3, 100 classes, random-init",
         "cifar_res32x4_res8x4_dkd_base": "DKD (base trainer, SGD) ResNet32x4->ResNet8x4, synthetic CIFAR-100 32x32x3, random-init",
+        "cifar_wrn40_2_wrn16_2_dkd_base": "DKD (base trainer, SGD) WRN-40-2->WRN-16-2, synthetic CIFAR-100 32x32x3, random-init",
+        "cifar_vgg13_vgg8_dkd_base": "DKD (base trainer, SGD) VGG13->VGG8, synthetic CIFAR-100 32x32x3, random-init",
     }
     return f"{name}: {labels.get(name, name)}"
 
@@ -108,6 +110,8 @@ def cpu_arm(workload: str, batch: int, steps: int, warmup: int, device: str = "c
     opt = oracle.DotListOracle([p.data for p in params], lr=cfg.SOLVER.LR, momentum=m - d, momentum_kd=m + d,
                                weight_decay=cfg.SOLVER.WEIGHT_DECAY)
     kind = cfg.DISTILLER.TYPE
+    base_trainer = cfg.SOLVER.TRAINER == "base"
+    sgd = torch.optim.SGD(params, lr=cfg.SOLVER.LR, momentum=m, weight_decay=cfg.SOLVER.WEIGHT_DECAY)
     image, target, _ = W.synthetic_batch(batch, hw, classes, seed=1234, device=device)
     on_gpu = str(device) != "cpu"
 
@@ -121,10 +125,15 @@ def cpu_arm(workload: str, batch: int, steps: int, warmup: int, device: str = "c
         else:
             l_ce = cfg.KD.LOSS.CE_WEIGHT * oracle.ce_loss(zs, target)
             l_kd = cfg.KD.LOSS.KD_WEIGHT * oracle.kd_loss(zs, zt, cfg.KD.TEMPERATURE)
-        g_kd = torch.autograd.grad(l_kd, params, retain_graph=True)
-        opt.step_kd(list(g_kd))
-        g_ce = torch.autograd.grad(l_ce, params)
-        opt.step(list(g_ce))
+        if base_trainer:        # BaseTrainer.train_iter (trainer.py:257-321): summed loss, one backward, optim.SGD
+            sgd.zero_grad()
+            (l_kd + l_ce).backward()
+            sgd.step()
+        else:                   # DOT.train_iter (trainer.py:412-432)
+            g_kd = torch.autograd.grad(l_kd, params, retain_graph=True)
+            opt.step_kd(list(g_kd))
+            g_ce = torch.autograd.grad(l_ce, params)
+            opt.step(list(g_ce))
         return l_kd.item() + l_ce.item()      # the reference reads its losses back every iteration too
 
     for _ in range(warmup):

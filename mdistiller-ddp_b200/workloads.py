@@ -6,9 +6,10 @@ The distillation tail treats backbones as opaque ``nn.Module``s returning
 (out of scope here).  The GPU box has no copy of the reference, so
 the benchmark instantiates architecture-equivalent stand-ins: torchvision's ResNet-18/
 34/50 for the ImageNet configs (same parameter counts as the reference's
-models/imagenet/resnet.py: 11 689 512 / 21 797 672 / 25 557 032) and a small
-CIFAR-style residual net for the ``resnet8x4`` / ``resnet32x4`` configs
-(1 233 540 / 7 433 860 parameters, as the reference's).  Weights are random-init.
+models/imagenet/resnet.py: 11 689 512 / 21 797 672 / 25 557 032) and small CIFAR-style
+nets written here for the ``resnet8x4`` / ``resnet32x4`` (1 233 540 / 7 433 860 parameters),
+``wrn_16_2`` / ``wrn_40_2`` (703 284 / 2 255 156) and ``vgg8`` / ``vgg13`` (3 965 028 / 9 462 180)
+configs -- the reference's parameter counts.  Weights are random-init.
 """
 
 from __future__ import annotations
@@ -85,6 +86,72 @@ def cifar_resnet(name: str, num_classes: int = 100) -> nn.Module:
     return CifarResNet(depth, (32, 64, 128, 256), num_classes)
 
 
+class _PreActUnit(nn.Module):
+    """Wide-ResNet unit: bn-relu-conv twice, 1x1 projection on the skip when the width changes."""
+
+    def __init__(self, cin: int, cout: int, stride: int):
+        super().__init__()
+        self.n1, self.c1 = nn.BatchNorm2d(cin), nn.Conv2d(cin, cout, 3, stride, 1, bias=False)
+        self.n2, self.c2 = nn.BatchNorm2d(cout), nn.Conv2d(cout, cout, 3, 1, 1, bias=False)
+        self.proj = nn.Conv2d(cin, cout, 1, stride, 0, bias=False) if cin != cout else None
+
+    def forward(self, x):
+        a = F.relu(self.n1(x))
+        y = self.c2(F.relu(self.n2(self.c1(a))))
+        return y + (x if self.proj is None else self.proj(a))
+
+
+class CifarWRN(nn.Module):
+    """WRN-depth-k for 32x32 inputs (depth = 6n+4): wrn_16_2 has 703 284 parameters, wrn_40_2 2 255 156."""
+
+    def __init__(self, depth: int, widen: int, num_classes: int = 100):
+        super().__init__()
+        assert (depth - 4) % 6 == 0
+        n = (depth - 4) // 6
+        widths = [16, 16 * widen, 32 * widen, 64 * widen]
+        self.stem = nn.Conv2d(3, widths[0], 3, 1, 1, bias=False)
+        units, cin = [], widths[0]
+        for stage, cout in enumerate(widths[1:]):
+            for u in range(n):
+                units.append(_PreActUnit(cin, cout, 2 if (u == 0 and stage > 0) else 1))
+                cin = cout
+        self.units = nn.Sequential(*units)
+        self.norm = nn.BatchNorm2d(cin)
+        self.head = nn.Linear(cin, num_classes)
+
+    def forward(self, x):
+        x = F.relu(self.norm(self.units(self.stem(x))))
+        pooled = torch.flatten(F.adaptive_avg_pool2d(x, 1), 1)
+        return self.head(pooled), {"pooled_feat": pooled}
+
+
+class CifarVGG(nn.Module):
+    """VGG-bn for 32x32 inputs, one Linear head: vgg8 has 3 965 028 parameters, vgg13 9 462 180."""
+
+    def __init__(self, convs_per_stage, num_classes: int = 100):
+        super().__init__()
+        layers, cin = [], 3
+        for stage, (reps, cout) in enumerate(zip(convs_per_stage, (64, 128, 256, 512, 512))):
+            for _ in range(reps):
+                layers += [nn.Conv2d(cin, cout, 3, padding=1), nn.BatchNorm2d(cout), nn.ReLU(inplace=True)]
+                cin = cout
+            if stage < 4:
+                layers.append(nn.MaxPool2d(2, 2))
+        self.features = nn.Sequential(*layers)
+        self.head = nn.Linear(512, num_classes)
+
+    def forward(self, x):
+        pooled = torch.flatten(F.adaptive_avg_pool2d(self.features(x), 1), 1)
+        return self.head(pooled), {"pooled_feat": pooled}
+
+
+def cifar_misc(name: str, num_classes: int = 100) -> nn.Module:
+    if name.startswith("wrn"):
+        depth, widen = {"wrn_16_2": (16, 2), "wrn_40_2": (40, 2)}[name]
+        return CifarWRN(depth, widen, num_classes)
+    return CifarVGG({"vgg8": (1, 1, 1, 1, 1), "vgg13": (2, 2, 2, 2, 2)}[name], num_classes)
+
+
 class TinyNet(nn.Module):
     """A few thousand parameters; for smoke() and unit tests."""
 
@@ -105,6 +172,9 @@ WORKLOADS = {
     "imagenet_r34_r18_kd_dot": ("ResNet34", "ResNet18", imagenet_resnet, 224, 1000, "KD", "dot", 256),
     "cifar_res32x4_res8x4_kd_dot": ("resnet32x4", "resnet8x4", cifar_resnet, 32, 100, "KD", "dot", 64),
     "cifar_res32x4_res8x4_dkd_base": ("resnet32x4", "resnet8x4", cifar_resnet, 32, 100, "DKD", "base", 64),
+    # BASELINE.json configs[2]: DKD, base trainer, 128 images per GPU
+    "cifar_wrn40_2_wrn16_2_dkd_base": ("wrn_40_2", "wrn_16_2", cifar_misc, 32, 100, "DKD", "base", 128),
+    "cifar_vgg13_vgg8_dkd_base": ("vgg13", "vgg8", cifar_misc, 32, 100, "DKD", "base", 128),
 }
 
 
@@ -117,7 +187,9 @@ def default_cfg(workload: str = "imagenet_r34_r18_dkd_dot") -> SimpleNamespace:
     return ns(
         EXPERIMENT=ns(AMP=False),
         DISTILLER=ns(TYPE=WORKLOADS[workload][5]),
-        DKD=ns(CE_WEIGHT=1.0, ALPHA=1.0, BETA=0.5 if imagenet else 8.0, T=1.0 if imagenet else 4.0,
+        DKD=ns(CE_WEIGHT=1.0, ALPHA=1.0,
+               BETA=0.5 if imagenet else (6.0 if ("wrn" in workload or "vgg" in workload) else 8.0),   # yaml values
+               T=1.0 if imagenet else 4.0,
                WARMUP=1 if imagenet else 20),
         KD=ns(TEMPERATURE=1 if imagenet else 4,
               LOSS=ns(CE_WEIGHT=0.5 if imagenet else 0.1, KD_WEIGHT=0.5 if imagenet else 0.9)),

@@ -33,3 +33,19 @@ def test_reference_arm_line_has_the_contract_keys():
 
 def test_reference_arm_other_ranks_print_nothing():
     assert _run("--workload", "cifar_res32x4_res8x4_kd_dot", env={"RANK": "1", "WORLD_SIZE": "2"}) == []
+
+
+def test_stand_in_backbones_have_the_reference_parameter_counts():
+    """SURVEY.md Appendix B (counted on the reference's own constructors)."""
+    import sys
+    sys.path.insert(0, ROOT)
+    from mdistiller_ddp_b200 import workloads as W
+    want = {"resnet8x4": 1_233_540, "resnet32x4": 7_433_860, "wrn_16_2": 703_284, "wrn_40_2": 2_255_156,
+            "vgg8": 3_965_028, "vgg13": 9_462_180}
+    for name, n in want.items():
+        net = W.cifar_resnet(name) if name.startswith("resnet") else W.cifar_misc(name)
+        assert sum(p.numel() for p in net.parameters()) == n, name
+    for name, n in (("ResNet18", 11_689_512), ("ResNet34", 21_797_672)):
+        assert sum(p.numel() for p in W.imagenet_resnet(name).parameters()) == n
+    assert set(W.WORKLOADS) >= {"imagenet_r34_r18_dkd_dot", "cifar_res32x4_res8x4_kd_dot", "cifar_res32x4_res8x4_dkd_base",
+                                "cifar_wrn40_2_wrn16_2_dkd_base", "cifar_vgg13_vgg8_dkd_base"}
