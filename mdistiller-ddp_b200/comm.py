@@ -82,6 +82,16 @@ class SymmetricShardComm(ShardComm):
         self.barrier_timeout_ms = barrier_timeout_ms
         self._handles = {}
 
+    def probe(self) -> None:
+        """Collective: allocate and rendezvous a tiny symmetric buffer, so that a box without NVLink
+        symmetric memory fails HERE (where the caller can still fall back to NCCL) and not half-way through
+        adopting the parameters."""
+        dev = torch.device("cuda", torch.cuda.current_device())
+        t = self.alloc_flat(1024, dev)
+        if self.use_multicast and not self.addresses(t)[0]:
+            raise RuntimeError("no NVSwitch multicast address for symmetric memory on this box")
+        self._handles.pop(t.data_ptr(), None)
+
     def alloc_flat(self, n: int, device: torch.device) -> torch.Tensor:
         """Collective: every rank must allocate the same sequence of buffers."""
         import torch.distributed._symmetric_memory as symm_mem

@@ -436,7 +436,7 @@ __global__ void __launch_bounds__(kLossThreads) loss_rows_generic(const LossArgs
     for (long long r = blockIdx.x; r < A.rows; r += gridDim.x) {
         const float *zs = A.zs + r * A.ld_s;
         const float *zt = A.zt + r * A.ld_t;
-        const long long gl = A.target[r];
+        const long long gl = (DKD || CE != 0) ? A.target[r] : -1;   // KD without CE may come with target == NULL
         const int g = (gl >= 0 && gl < A.classes) ? (int)gl : -1;
         const float zsg = g >= 0 ? __ldg(zs + g) : kNegBig;
         const float ztg = g >= 0 ? __ldg(zt + g) : kNegBig;
@@ -517,89 +517,129 @@ __global__ void scale_by_scalar_kernel(float *out, const float *g, const float *
 // ---------------------------------------------------------------------------------------
 // host-side dispatch
 // ---------------------------------------------------------------------------------------
-// Resident CTAs per SM of a kernel at kLossThreads threads (register-limited); looked up once.
+// Launch context of one entry-point call: the current device, its SM count, the stream, and whether the
+// scratch's arrival counter has to be cleared before the kernel (static scratch: it may hold leftovers).
+struct LaunchCtx {
+    int dev, sms;
+    cudaStream_t st;
+    bool clear_ticket;
+};
+
+// Everything cached about a kernel is cached PER DEVICE: the dynamic shared-memory opt-in
+// (cudaFuncSetAttribute) and the occupancy answer both belong to the device that was current when they
+// were made, and one process may drive several GPUs.  One mutex guards all the small tables.
+constexpr int kMaxDevices = 64;
+static std::mutex s_kernel_cache_mutex;
+
+struct PerDeviceInt {
+    int v[kMaxDevices];   // 0 = not looked up yet
+};
+
+// Resident CTAs per SM of a kernel at kLossThreads threads and `smem` dynamic bytes; looked up once per device
+// (and again whenever `smem` grows, for the staged kernels).
 template <typename Kernel>
-static int resident_ctas_per_sm(Kernel kernel) {
+static int resident_ctas_per_sm(Kernel kernel, int dev, size_t smem, PerDeviceInt &cache, PerDeviceInt *smem_seen = nullptr) {
+    const int d = (dev >= 0 && dev < kMaxDevices) ? dev : 0;
+    std::lock_guard<std::mutex> lock(s_kernel_cache_mutex);
+    if (cache.v[d] > 0 && (!smem_seen || smem_seen->v[d] == (int)smem)) return cache.v[d];
     int n = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kLossThreads, 0) != cudaSuccess || n < 1) n = 1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kLossThreads, smem) != cudaSuccess || n < 1) n = 1;
+    cache.v[d] = n;
+    if (smem_seen) smem_seen->v[d] = (int)smem;
     return n;
+}
+
+// Dynamic shared memory above 48 KB needs an opt-in per kernel AND per device.
+template <typename Kernel>
+static cudaError_t ensure_dynamic_smem(Kernel kernel, int dev, size_t smem, PerDeviceInt &configured) {
+    const int d = (dev >= 0 && dev < kMaxDevices) ? dev : 0;
+    std::lock_guard<std::mutex> lock(s_kernel_cache_mutex);
+    if ((size_t)configured.v[d] >= smem) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) configured.v[d] = (int)smem;
+    return e;
+}
+
+// Grid fits the scratch?  Then (static scratch only) clear the arrival counter on the stream, right before the
+// kernel -- a refused call must not have queued anything.
+static cudaError_t before_launch(const LossArgs &A, const LaunchCtx &ctx, long long grid) {
+    if (grid > A.slots) return kGridExceedsSlots;
+    if (ctx.clear_ticket) return cudaMemsetAsync(A.ticket, 0, kWorkspaceHeader, ctx.st);
+    return cudaSuccess;
 }
 
 // Persistent grid: never more CTAs than the chip holds at once, so every CTA loops over an
 // (almost) equal share of the rows and there is no partial last wave.
 template <int LPR, int NV, bool DKD, int CE, bool SPLIT>
-static cudaError_t launch_regs(const LossArgs &A, int sms, cudaStream_t st) {
+static cudaError_t launch_regs(const LossArgs &A, const LaunchCtx &ctx) {
     constexpr int rows_per_cta = kLossWarps * (32 / LPR);
-    static const int occ = resident_ctas_per_sm(loss_rows_in_registers<LPR, NV, DKD, CE, SPLIT>);
+    static PerDeviceInt occ_cache;
+    const int occ = resident_ctas_per_sm(loss_rows_in_registers<LPR, NV, DKD, CE, SPLIT>, ctx.dev, 0, occ_cache);
     long long want = (A.rows + rows_per_cta - 1) / rows_per_cta;
-    const long long cap = (long long)sms * occ;
+    const long long cap = (long long)ctx.sms * occ;
     if (want > cap) want = cap;
     if (want > kMaxCtas) want = kMaxCtas;
-    if (want > A.slots) return kGridExceedsSlots;
-    loss_rows_in_registers<LPR, NV, DKD, CE, SPLIT><<<(unsigned)want, kLossThreads, 0, st>>>(A);
+    if (cudaError_t e = before_launch(A, ctx, want)) return e;
+    loss_rows_in_registers<LPR, NV, DKD, CE, SPLIT><<<(unsigned)want, kLossThreads, 0, ctx.st>>>(A);
     return cudaGetLastError();
 }
 
 template <int LPR, int NV, bool DKD, int CE, bool SPLIT>
-static cudaError_t launch_staged(const LossArgs &A, int sms, cudaStream_t st) {
+static cudaError_t launch_staged(const LossArgs &A, const LaunchCtx &ctx) {
     constexpr int GPW = 32 / LPR;
     constexpr int rows_per_cta = kLossWarps * GPW;
     auto kernel = loss_rows_in_registers<LPR, NV, DKD, CE, SPLIT, true>;
     const size_t region = (2 * (size_t)GPW * A.classes * sizeof(float) + 127) & ~(size_t)127;
     const size_t smem = 128 + kLossWarps * region;
-    static size_t configured = 0;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = smem;
-    }
-    int occ = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kLossThreads, smem) != cudaSuccess || occ < 1) occ = 1;
+    static PerDeviceInt configured, occ_cache, occ_smem;
+    if (cudaError_t e = ensure_dynamic_smem(kernel, ctx.dev, smem, configured)) return e;
+    const int occ = resident_ctas_per_sm(kernel, ctx.dev, smem, occ_cache, &occ_smem);
     long long want = (A.rows + rows_per_cta - 1) / rows_per_cta;
-    const long long cap = (long long)sms * occ;
+    const long long cap = (long long)ctx.sms * occ;
     if (want > cap) want = cap;
     if (want > kMaxCtas) want = kMaxCtas;
-    if (want > A.slots) return kGridExceedsSlots;
-    kernel<<<(unsigned)want, kLossThreads, smem, st>>>(A);
+    if (cudaError_t e = before_launch(A, ctx, want)) return e;
+    kernel<<<(unsigned)want, kLossThreads, smem, ctx.st>>>(A);
     return cudaGetLastError();
 }
 
 template <bool DKD, int CE, bool SPLIT>
-static cudaError_t launch_shape(const LossArgs &A, bool vec_ok, int sms, cudaStream_t st) {
+static cudaError_t launch_shape(const LossArgs &A, bool vec_ok, const LaunchCtx &ctx) {
     const long long nvec = A.classes >> 2;
     // TMA-staged variants where they measured faster (B200): narrow rows at any batch (65536x100: -9 %), 1000-class
     // rows up to mid-size batches (4096x1000: -10 %, 16384x1000: -3 %; +4.5 % at 65536x1000, so not there).
     // MDB200_LOSS_STAGED=0 switches them off for A/B timing.
     static const bool staged = !(getenv("MDB200_LOSS_STAGED") && atoi(getenv("MDB200_LOSS_STAGED")) == 0);
     if (staged && vec_ok && A.ld_s == A.classes && A.ld_t == A.classes) {
-        if (nvec <= 28) return launch_staged<4, 7, DKD, CE, SPLIT>(A, sms, st);
-        if (nvec <= 32) return launch_staged<8, 4, DKD, CE, SPLIT>(A, sms, st);
-        if (nvec > 128 && nvec <= 256 && A.rows <= 32768) return launch_staged<32, 8, DKD, CE, SPLIT>(A, sms, st);
+        if (nvec <= 28) return launch_staged<4, 7, DKD, CE, SPLIT>(A, ctx);
+        if (nvec <= 32) return launch_staged<8, 4, DKD, CE, SPLIT>(A, ctx);
+        if (nvec > 128 && nvec <= 256 && A.rows <= 32768) return launch_staged<32, 8, DKD, CE, SPLIT>(A, ctx);
     }
-    if (vec_ok && nvec <= 28) return launch_regs<4, 7, DKD, CE, SPLIT>(A, sms, st);     // classes <= 112 (CIFAR-100: 25 of 28 slots)
-    if (vec_ok && nvec <= 32) return launch_regs<8, 4, DKD, CE, SPLIT>(A, sms, st);
-    if (vec_ok && nvec <= 128) return launch_regs<32, 4, DKD, CE, SPLIT>(A, sms, st);
-    if (vec_ok && nvec <= 256) return launch_regs<32, 8, DKD, CE, SPLIT>(A, sms, st);   // ImageNet-1k: 250 of 256 slots
+    if (vec_ok && nvec <= 28) return launch_regs<4, 7, DKD, CE, SPLIT>(A, ctx);     // classes <= 112 (CIFAR-100: 25 of 28 slots)
+    if (vec_ok && nvec <= 32) return launch_regs<8, 4, DKD, CE, SPLIT>(A, ctx);
+    if (vec_ok && nvec <= 128) return launch_regs<32, 4, DKD, CE, SPLIT>(A, ctx);
+    if (vec_ok && nvec <= 256) return launch_regs<32, 8, DKD, CE, SPLIT>(A, ctx);   // ImageNet-1k: 250 of 256 slots
     if constexpr (CE != 2) {  // a third 64-float register row would spill: general-T CE goes generic there
-        if (vec_ok && nvec <= 512) return launch_regs<32, 16, DKD, CE, SPLIT>(A, sms, st);
+        if (vec_ok && nvec <= 512) return launch_regs<32, 16, DKD, CE, SPLIT>(A, ctx);
     }
-    static const int occ = resident_ctas_per_sm(loss_rows_generic<DKD, CE, SPLIT>);
+    static PerDeviceInt occ_cache;
+    const int occ = resident_ctas_per_sm(loss_rows_generic<DKD, CE, SPLIT>, ctx.dev, 0, occ_cache);
     long long want = A.rows;
-    const long long cap = (long long)sms * occ;
+    const long long cap = (long long)ctx.sms * occ;
     if (want > cap) want = cap;
     if (want > kMaxCtas) want = kMaxCtas;
-    if (want > A.slots) return kGridExceedsSlots;
-    loss_rows_generic<DKD, CE, SPLIT><<<(unsigned)want, kLossThreads, 0, st>>>(A);
+    if (cudaError_t e = before_launch(A, ctx, want)) return e;
+    loss_rows_generic<DKD, CE, SPLIT><<<(unsigned)want, kLossThreads, 0, ctx.st>>>(A);
     return cudaGetLastError();
 }
 
 template <bool DKD>
-static cudaError_t launch_ce(const LossArgs &A, int ce, bool split, bool vec_ok, int sms, cudaStream_t st) {
-    if (ce == 0) return launch_shape<DKD, 0, false>(A, vec_ok, sms, st);
-    if (ce == 1) return split ? launch_shape<DKD, 1, true>(A, vec_ok, sms, st)
-                              : launch_shape<DKD, 1, false>(A, vec_ok, sms, st);
-    return split ? launch_shape<DKD, 2, true>(A, vec_ok, sms, st)
-                 : launch_shape<DKD, 2, false>(A, vec_ok, sms, st);
+static cudaError_t launch_ce(const LossArgs &A, int ce, bool split, bool vec_ok, const LaunchCtx &ctx) {
+    if (ce == 0) return launch_shape<DKD, 0, false>(A, vec_ok, ctx);
+    if (ce == 1) return split ? launch_shape<DKD, 1, true>(A, vec_ok, ctx)
+                              : launch_shape<DKD, 1, false>(A, vec_ok, ctx);
+    return split ? launch_shape<DKD, 2, true>(A, vec_ok, ctx)
+                 : launch_shape<DKD, 2, false>(A, vec_ok, ctx);
 }
 
 }  // namespace mdb200
@@ -608,6 +648,16 @@ using namespace mdb200;
 
 extern "C" size_t mdb200_loss_workspace_bytes(void) {
     return kWorkspaceHeader + 2 * (size_t)kMaxCtas * sizeof(double);
+}
+
+static LaunchCtx make_launch_ctx(void *stream, bool clear_ticket) {
+    LaunchCtx ctx;
+    ctx.dev = 0;
+    if (cudaGetDevice(&ctx.dev) != cudaSuccess) ctx.dev = 0;
+    ctx.sms = sm_count();
+    ctx.st = reinterpret_cast<cudaStream_t>(stream);
+    ctx.clear_ticket = clear_ticket;
+    return ctx;
 }
 
 // Argument checks and LossArgs set-up shared by the two loss entry points; the scratch
@@ -669,10 +719,9 @@ extern "C" int mdb200_distill_loss(const float *z_student, const float *z_teache
     A.ticket = reinterpret_cast<unsigned *>(workspace);
     A.part = reinterpret_cast<double *>(reinterpret_cast<char *>(workspace) + kWorkspaceHeader);
     A.slots = kMaxCtas;
-    const int sms = sm_count();
-    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    cudaError_t e = (kind == MDB200_LOSS_DKD) ? launch_ce<true>(A, ce, split, vec_ok, sms, st)
-                                              : launch_ce<false>(A, ce, split, vec_ok, sms, st);
+    const LaunchCtx ctx = make_launch_ctx(stream, false);
+    cudaError_t e = (kind == MDB200_LOSS_DKD) ? launch_ce<true>(A, ce, split, vec_ok, ctx)
+                                              : launch_ce<false>(A, ce, split, vec_ok, ctx);
     return (int)e;
 }
 
@@ -693,7 +742,6 @@ constexpr int kStaticSlots = MDB200_STATIC_SCRATCH_CTAS;
 constexpr size_t kStaticScratchBytes = kWorkspaceHeader + 2 * (size_t)kStaticSlots * sizeof(double);
 static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
 
-constexpr int kMaxDevices = 64;
 static void *s_static_scratch_ptr[kMaxDevices];   // per-device address of g_static_scratch, 0 = not resolved yet
 static std::mutex s_static_scratch_mutex;
 
@@ -730,17 +778,16 @@ extern "C" int mdb200_distill_loss_static_scratch(const float *z_student, const 
     void *scratch = nullptr;
     rc = static_scratch_for_current_device(&scratch);
     if (rc != 0) return rc;
-    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     // The array keeps whatever the previous call (or an aborted one) left behind; only the
     // arrival counter in the header has to start at zero, the partial sums are overwritten.
-    cudaError_t e = cudaMemsetAsync(scratch, 0, kWorkspaceHeader, st);
-    if (e != cudaSuccess) return (int)e;
+    // The launcher clears it on `stream` once it knows the grid fits (clear_ticket), so a
+    // refused call has queued nothing and touched nothing.
     A.ticket = reinterpret_cast<unsigned *>(scratch);
     A.part = reinterpret_cast<double *>(reinterpret_cast<char *>(scratch) + kWorkspaceHeader);
     A.slots = kStaticSlots;
-    const int sms = sm_count();
-    e = (kind == MDB200_LOSS_DKD) ? launch_ce<true>(A, ce, split, vec_ok, sms, st)
-                                  : launch_ce<false>(A, ce, split, vec_ok, sms, st);
+    const LaunchCtx ctx = make_launch_ctx(stream, true);
+    cudaError_t e = (kind == MDB200_LOSS_DKD) ? launch_ce<true>(A, ce, split, vec_ok, ctx)
+                                              : launch_ce<false>(A, ce, split, vec_ok, ctx);
     if (e == kGridExceedsSlots) return MDB200_ESCRATCH;
     return (int)e;
 }

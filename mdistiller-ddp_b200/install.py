@@ -53,6 +53,10 @@ def install(replace_base: bool = True):
             self.grad_clip = cfg.SOLVER.GRAD_CLIP       # needed by init_optimizer's callers early (D1)
             self.use_amp = cfg.EXPERIMENT.AMP
             base.__init__(self, experiment_name, distiller, train_loader, val_loader, cfg)
+            # lets train_iter know when an epoch ends: lagged metrics are settled and the sharded optimizer
+            # state is snapshotted on every rank, so train_epoch (trainer.py:188-255 of the reference, unchanged)
+            # can read exact averages and call optimizer.state_dict() on the master rank alone
+            self.iters_per_epoch = len(train_loader)
 
     class DOT(_RefHosted):
         trainer_kind = "dot"

@@ -67,6 +67,9 @@ class _FlatOptimizer(Optimizer):
         self._index = {id(p): i for i, p in enumerate(plist)}
         self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in plist if p.requires_grad]
         self._run_cache: Dict[tuple, list] = {}
+        self._n_steps = 0                       # completed step() calls; dates the checkpoint snapshot
+        self._snapshot: Optional[Dict[str, torch.Tensor]] = None
+        self._snapshot_step = -1
 
     # -- gradient capture ----------------------------------------------------------
     def _on_grad(self, p: torch.Tensor) -> None:
@@ -189,12 +192,36 @@ class _FlatOptimizer(Optimizer):
         self._comm.all_gather(full)
         return full
 
+    def _state_pairs(self) -> Sequence[Tuple[str, torch.Tensor, List[bool]]]:
+        """(checkpoint key, sharded buffer, per-parameter "exists" flags) of every state tensor."""
+        raise NotImplementedError
+
+    def sync_checkpoint_state(self) -> None:
+        """COLLECTIVE -- call on every rank.  Gathers the sharded optimizer state into a full-length
+        snapshot so that a later ``state_dict()`` on any ONE rank needs no communication.
+
+        Why it exists: the reference asks only the master rank for ``optimizer.state_dict()``
+        (mdistiller/engine/trainer.py:230-236, under ``if IS_MASTER``), which is fine for a replicated
+        torch optimizer but would leave rank 0 alone inside an all-gather when the momenta are sharded.
+        The hosted trainers call this after the last iteration of every epoch (trainer.py here), so the
+        reference's epoch loop checkpoints unchanged.  The snapshot is dropped by the next ``step()``."""
+        if self._comm.world_size == 1:
+            return
+        self._snapshot = {key: self._full_momentum(buf) for key, buf, has in self._state_pairs() if any(has)}
+        self._snapshot_step = self._n_steps
+
     def _export_state(self, pairs: Sequence[Tuple[str, torch.Tensor, List[bool]]]) -> None:
+        sharded = self._comm.world_size > 1
+        if sharded and (self._snapshot is None or self._snapshot_step != self._n_steps):
+            raise RuntimeError(
+                "optimizer state is sharded over ranks: call optimizer.sync_checkpoint_state() on EVERY rank "
+                "(after the last step) before state_dict(); state_dict() itself never communicates, so it is "
+                "safe on one rank, as the reference's master-only checkpointing needs")
         self.state.clear()
         for key, shard_buf, has in pairs:
             if not any(has):
                 continue
-            full = self._full_momentum(shard_buf)
+            full = self._snapshot[key] if sharded else shard_buf     # world 1: the shard IS the full buffer
             for p, v, h in zip(self._space.params, self._space.views(full), has):
                 if h:
                     self.state[p][key] = v.clone()
@@ -280,10 +307,10 @@ class DistillationOrientedTrainer(_FlatOptimizer):
         sp = self._space
         momentum = group["momentum"]
         steady = (self._steady and task_members is self._all_true and kd_members is self._all_true)
+        modes: list = []
         if steady:      # every parameter in both lists and every buffer already exists: one cached run
             runs = self._steady_runs
         else:
-            modes = []
             for i, (t, k) in enumerate(zip(task_members, kd_members)):
                 m = (_BOTH if k else _TASK) if t else (_KD if k else _NONE)
                 modes.append((m, t and not self._has_vt[i], k and not self._has_vk[i]))
@@ -291,11 +318,14 @@ class DistillationOrientedTrainer(_FlatOptimizer):
         hp = dict(lr=group["lr"], momentum=momentum, momentum_kd=group["momentum_kd"],
                   weight_decay=group["weight_decay"], dampening=group["dampening"],
                   grad_scale=1.0 / self._comm.world_size)
-        fused = (getattr(self._comm, "fused", False) and self._comm.world_size > 1 and len(runs) == 1
-                 and runs[0][0] == sp.shard_lo and runs[0][1] == sp.shard_hi and runs[0][2][0] == _BOTH
+        # The fused kernel is a rendezvous of ALL ranks, so the decision must come out the same everywhere:
+        # it is taken from the global membership (every tensor in both lists, identical first-step flags),
+        # never from `runs`, which is clipped to this rank's shard and may look uniform on one rank only.
+        uniform = steady or (len(modes) > 0 and modes[0][0] == _BOTH and all(m == modes[0] for m in modes))
+        fused = (getattr(self._comm, "fused", False) and self._comm.world_size > 1 and uniform
                  and self._kd_members is not None)
         if fused:
-            self._fused_step(runs[0][2], hp)
+            self._fused_step(modes[0] if not steady else (_BOTH, False, False), hp)
         else:
             if getattr(self, "_kd_prereduced", True) is False:   # KD bucket was left for a fused step that cannot run
                 self._kd_work = self._comm.reduce_scatter_sum(self._buckets["kd"], async_op=True)
@@ -326,6 +356,8 @@ class DistillationOrientedTrainer(_FlatOptimizer):
                 self._steady_runs = self._runs([(_BOTH, False, False)] * len(self._has_vk))
         self._kd_members = None
         self._phase = "kd"
+        self._n_steps += 1
+        self._snapshot = None
         return loss
 
     def _fused_step(self, mode, hp) -> None:
@@ -349,9 +381,11 @@ class DistillationOrientedTrainer(_FlatOptimizer):
         comm.barrier(p, channel=1)          # nobody reads P before every shard owner has written it
 
     # -- reference checkpoint layout: state[p]['momentum_buffer'|'momentum_kd_buffer'] -----
+    def _state_pairs(self):
+        return (("momentum_buffer", self._v_task, self._has_vt), ("momentum_kd_buffer", self._v_kd, self._has_vk))
+
     def state_dict(self):
-        self._export_state((("momentum_buffer", self._v_task, self._has_vt),
-                            ("momentum_kd_buffer", self._v_kd, self._has_vk)))
+        self._export_state(self._state_pairs())
         try:
             return super().state_dict()
         finally:
@@ -359,10 +393,10 @@ class DistillationOrientedTrainer(_FlatOptimizer):
 
     def load_state_dict(self, state_dict):
         super().load_state_dict(state_dict)
-        self._import_state((("momentum_buffer", self._v_task, self._has_vt),
-                            ("momentum_kd_buffer", self._v_kd, self._has_vk)))
+        self._import_state(self._state_pairs())
         self._run_cache.clear()
         self._steady = False
+        self._snapshot = None
 
     def momentum_views(self):
         """Per-parameter views of the (unsharded) momentum buffers -- single-process use."""
@@ -419,10 +453,15 @@ class FlatSGD(_FlatOptimizer):
             for i, t in enumerate(members):
                 if t:
                     self._has_v[i] = True
+        self._n_steps += 1
+        self._snapshot = None
         return loss
 
+    def _state_pairs(self):
+        return (("momentum_buffer", self._v, self._has_v),)
+
     def state_dict(self):
-        self._export_state((("momentum_buffer", self._v, self._has_v),))
+        self._export_state(self._state_pairs())
         try:
             return super().state_dict()
         finally:
@@ -430,8 +469,9 @@ class FlatSGD(_FlatOptimizer):
 
     def load_state_dict(self, state_dict):
         super().load_state_dict(state_dict)
-        self._import_state((("momentum_buffer", self._v, self._has_v),))
+        self._import_state(self._state_pairs())
         self._run_cache.clear()
+        self._snapshot = None
 
 
 class FlatAdam(_FlatOptimizer):
@@ -487,11 +527,16 @@ class FlatAdam(_FlatOptimizer):
                               weight_decay=group["weight_decay"], decoupled=self.decoupled, step=step,
                               grad_scale=1.0 / self._comm.world_size, grad_scale_dev=clip)
         self._comm.all_gather(sp.flat)
+        self._n_steps += 1
+        self._snapshot = None
         return loss
 
-    def state_dict(self):
+    def _state_pairs(self):
         has = [n > 0 for n in self._steps]
-        self._export_state((("exp_avg", self._m, has), ("exp_avg_sq", self._v, has)))
+        return (("exp_avg", self._m, has), ("exp_avg_sq", self._v, list(has)))
+
+    def state_dict(self):
+        self._export_state(self._state_pairs())
         for p, n in zip(self._space.params, self._steps):
             if n > 0:
                 self.state[p]["step"] = torch.tensor(float(n))
@@ -506,3 +551,4 @@ class FlatAdam(_FlatOptimizer):
         has = [False] * len(self._steps)
         self._import_state((("exp_avg", self._m, has), ("exp_avg_sq", self._v, list(has))))
         self._run_cache.clear()
+        self._snapshot = None

@@ -58,22 +58,38 @@ class TailStepMixin:
     ``self.distiller``, ``self.cfg`` and (after init) ``self.optimizer``."""
 
     trainer_kind = "dot"   # "dot" | "base"
-    # how the data-parallel DOT step talks: "nccl" = reduce-scatter / update / all-gather launches,
-    # "fused" = one kernel over NVLink symmetric memory (KD bucket still on an overlapped NCCL
-    # reduce-scatter), "fused_kd" = both buckets in the kernel, "*_p2p" = no NVSwitch multicast
-    comm_mode = os.environ.get("MDB200_COMM", "nccl")
+    # how the data-parallel step talks: "auto" (default) = the measured policy of resolve_comm_mode(), falling
+    # back to NCCL launches when NVLink symmetric memory cannot be set up; "nccl" = reduce-scatter / update /
+    # all-gather launches; "fused" = one kernel over NVLink symmetric memory (KD bucket still on an overlapped
+    # NCCL reduce-scatter); "fused_kd" = both buckets in the kernel; "*_p2p" = no NVSwitch multicast
+    comm_mode = os.environ.get("MDB200_COMM", "auto")
+    comm_mode_used = "none"       # what init_optimizer actually set up (bench.py reports it)
 
     # ---------------------------------------------------------------- optimizer
+    def _make_comm(self):
+        """The data-parallel plumbing this trainer ships with -- bench.py measures exactly this."""
+        if not (dist.is_available() and dist.is_initialized()):
+            self.comm_mode_used = "none"
+            return None
+        world = dist.get_world_size()
+        mode = resolve_comm_mode(self.comm_mode, world)
+        if mode != "nccl" and world > 1:
+            try:
+                comm = SymmetricShardComm(fuse_kd=mode.startswith("fused_kd"), use_multicast=not mode.endswith("p2p"))
+                comm.probe()                    # allocation + rendezvous work on this box?
+                self.comm_mode_used = mode
+                return comm
+            except Exception as e:              # no symmetric memory / multicast here
+                if self.comm_mode != "auto":
+                    raise
+                self.comm_fallback_reason = f"{type(e).__name__}: {str(e)[:160]}"
+        self.comm_mode_used = "nccl" if world > 1 else "none"
+        return ShardComm()
+
     def init_optimizer(self, cfg):
         core = _unwrap(self.distiller)
         silence_ddp_reducer(self.distiller)
-        comm = None
-        if dist.is_available() and dist.is_initialized():
-            mode = self.comm_mode
-            if mode != "nccl" and self.trainer_kind == "dot" and dist.get_world_size() > 1:
-                comm = SymmetricShardComm(fuse_kd=mode.startswith("fused_kd"), use_multicast=not mode.endswith("p2p"))
-            else:
-                comm = ShardComm()
+        comm = self._make_comm()
         params = core.get_learnable_parameters()
         if self.trainer_kind == "dot":
             if cfg.EXPERIMENT.AMP:
@@ -105,12 +121,30 @@ class TailStepMixin:
 
     # ---------------------------------------------------------------- one iteration
     # metrics_lag = 0: the progress line of an iteration contains that iteration (the reference's
-    # behaviour, one host sync per step).  metrics_lag = k > 0: the device-to-host read of step i is
-    # only waited for at step i+k, so the host can already enqueue the next batch's H2D copy and
-    # kernels while the GPU finishes step i; call flush_metrics() before reading the meters.
-    metrics_lag = 0
+    # behaviour, one host sync per step).  metrics_lag = k > 0 (default 1, MDB200_METRICS_LAG): the
+    # device-to-host read of step i is only waited for at step i+k, so the host can already enqueue the
+    # next batch's H2D copy and kernels while the GPU finishes step i; the progress line then trails by k
+    # iterations, and flush_metrics() (called automatically after an epoch's last iteration when the host
+    # set iters_per_epoch) settles the rest before anybody reads the epoch averages.
+    metrics_lag = int(os.environ.get("MDB200_METRICS_LAG", "1"))
+    # set by a host that knows the epoch length (install.py: len(train_loader)): after the epoch's last
+    # iteration every rank settles the lagged metrics and takes the collective checkpoint snapshot, so the
+    # reference's epoch loop can log exact averages and checkpoint on the master rank alone
+    iters_per_epoch = 0
 
     def train_iter(self, data, epoch, train_meters):
+        msg = self._train_iter(data, epoch, train_meters)
+        if self.iters_per_epoch:
+            if self.__dict__.get("_epoch_seen") != epoch:
+                self._epoch_seen, self._iter_in_epoch = epoch, 0
+            self._iter_in_epoch += 1
+            if self._iter_in_epoch == self.iters_per_epoch:
+                self.flush_metrics(train_meters)
+                self.optimizer.sync_checkpoint_state()
+                msg = self._progress_line(epoch, train_meters)
+        return msg
+
+    def _train_iter(self, data, epoch, train_meters):
         t0 = time.time()
         image, target, index = data
         train_meters["data_time"].update(time.time() - t0)
@@ -227,6 +261,17 @@ class TailStepMixin:
         return "Epoch:{}| Time(data):{:.3f}| Time(train):{:.3f}| Loss:{:.4f}| Top-1:{:.3f}| Top-5:{:.3f}".format(
             epoch, train_meters["data_time"].avg, train_meters["training_time"].avg, total,
             train_meters["top1"].avg, train_meters["top5"].avg)
+
+
+def resolve_comm_mode(mode: str, world: int) -> str:
+    """"auto" -> the step measured best on one HGX B200 box (profiles/): the fused NVLink kernel with plain peer
+    loads/stores up to 4 GPUs, NVSwitch multicast with both buckets in the kernel above; anything else is
+    taken literally."""
+    if mode != "auto":
+        return mode
+    if world <= 1:
+        return "nccl"
+    return "fused_p2p" if world <= 4 else "fused_kd"
 
 
 def _trust(opt):

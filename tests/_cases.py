@@ -50,6 +50,10 @@ LOSS_CASES: List[LossCase] = [
     LossCase("conf8_32x1000_T1", 21, 32, 1000, 3.0, 1.0, 0.5, 1.0, 8.0),
     LossCase("wide_48x100_s10", 22, 48, 100, 10.0, 1.0, 8.0, 4.0),
     LossCase("big_4096x100", 23, 4096, 100, 3.0, 1.0, 8.0, 4.0),
+    # 113..128 classes: the 8-lanes-per-row register layout (launch_shape's <8,4> branch)
+    LossCase("mid_96x116", 24, 96, 116, 3.0, 1.0, 8.0, 4.0),
+    LossCase("mid_64x120_T1", 25, 64, 120, 3.0, 1.0, 0.5, 1.0),
+    LossCase("mid_200x128", 26, 200, 128, 3.0, 1.0, 6.0, 2.0),
 ]
 
 

@@ -59,6 +59,56 @@ def test_100_step_trajectory_matches_reference(case, dot_golden, b200):
             assert oracle.max_rel_err(got, ref) <= TOL, (case.name, key, tag)
 
 
+def _dot_steps(case, opt, params, steps):
+    shapes = [p.shape for p in params]
+    for step in steps:
+        if step == case.lr_drop_at:
+            opt.param_groups[0]["lr"] = case.lr * 0.1
+        kd, task = _cases.make_grads(case, step, shapes)
+        opt.zero_grad(set_to_none=True)
+        for p, g in zip(params, kd):
+            p.grad = None if g is None else g.cuda()
+        opt.step_kd()
+        opt.zero_grad(set_to_none=True)
+        for p, g in zip(params, task):
+            p.grad = None if g is None else g.cuda()
+        opt.step()
+
+
+@pytest.mark.parametrize("name", ["dot_cifar_small", "dot_membership"])
+def test_checkpoint_on_cuda_has_the_reference_layout_and_momenta(name, dot_golden, b200):
+    """SURVEY 8 f-4 on the GPU: state_dict() after the fixture's 100 steps holds the reference's
+    'momentum_buffer' / 'momentum_kd_buffer' per parameter (dot.py:165-170) with the reference's values,
+    and a fresh optimizer that loads it continues bit-identically."""
+    case = next(c for c in _cases.DOT_CASES if c.name == name)
+    mk = lambda ps: b200.DistillationOrientedTrainer(ps, lr=case.lr, momentum=case.momentum - case.delta,
+                                                     momentum_kd=case.momentum + case.delta,
+                                                     dampening=case.dampening, weight_decay=case.wd)
+    params = [torch.nn.Parameter(p.clone().cuda()) for p in _cases.make_params(case)]
+    opt = mk(params)
+    _dot_steps(case, opt, params, range(case.steps))
+    sd = opt.state_dict()
+    assert all(t.is_cuda for st in sd["state"].values() for t in st.values())
+    for key, gkey in (("momentum_buffer", "vt64"), ("momentum_kd_buffer", "vk64")):
+        bufs = [sd["state"].get(i, {}).get(key) for i in range(len(params))]
+        missing = case.task_missing if key == "momentum_buffer" else case.kd_missing
+        assert [b is None for b in bufs] == [i in missing for i in range(len(params))]
+        got, ref = _ref(dot_golden, case.name, gkey, _flat(bufs, params))
+        assert oracle.max_rel_err(got, ref) <= TOL
+    params2 = [torch.nn.Parameter(p.detach().clone()) for p in params]
+    opt2 = mk(params2)
+    opt2.load_state_dict(sd)
+    assert opt2.param_groups[0]["lr"] == opt.param_groups[0]["lr"]
+    for o, ps in ((opt, params), (opt2, params2)):
+        _dot_steps(case, o, ps, range(case.steps, case.steps + 3))
+    for p, q in zip(params, params2):
+        assert torch.equal(p, q)
+    sd1, sd2 = opt.state_dict(), opt2.state_dict()
+    for i in sd1["state"]:
+        for k in sd1["state"][i]:
+            assert torch.equal(sd1["state"][i][k], sd2["state"][i][k])
+
+
 @pytest.mark.parametrize("case", [c for c in _cases.DOT_CASES if c.kind != "dot"], ids=lambda c: c.name)
 def test_base_optimizer_trajectories_match_torch(case, dot_golden, b200):
     """SGD / Adam / AdamW with and without global-norm clipping vs torch.optim + clip_grad_norm_
@@ -332,7 +382,7 @@ def test_lagged_metrics_account_every_iteration(b200):
     cfg = W.default_cfg("cifar_res32x4_res8x4_kd_dot")
     eager = b200.StandaloneTrainer(b200.KD(student, teacher, cfg).cuda().train(), cfg)
     lagged = b200.StandaloneTrainer(b200.KD(s2, t2, cfg).cuda().train(), cfg)
-    lagged.metrics_lag = 2
+    eager.metrics_lag, lagged.metrics_lag = 0, 2
     m1, m2 = b200.new_train_meters(), b200.new_train_meters()
     for step in range(5):
         batch = W.synthetic_batch(16, 32, 100, seed=60 + step, pin=True)
@@ -344,6 +394,25 @@ def test_lagged_metrics_account_every_iteration(b200):
     for k in ("loss_ce", "loss_kd", "_total"):
         assert abs(m1["losses"][k].avg - m2["losses"][k].avg) <= 1e-5 * abs(m1["losses"][k].avg)
     assert m1["top5"].avg == m2["top5"].avg
+
+
+def test_epoch_end_settles_metrics_and_checkpoint_snapshot(b200):
+    """A host that tells the mixin the epoch length (install.py does: len(train_loader)) gets exact meters and a
+    checkpointable optimizer right after the epoch's last train_iter -- what the reference's train_epoch reads
+    next (trainer.py:213-236) -- although metrics are read back one iteration late by default."""
+    from mdistiller_ddp_b200 import workloads as W
+    torch.manual_seed(6)
+    cfg = W.default_cfg("cifar_res32x4_res8x4_kd_dot")
+    tr = b200.StandaloneTrainer(b200.KD(W.TinyNet(100, 16), W.TinyNet(100, 24), cfg).cuda().train(), cfg)
+    assert tr.metrics_lag == 1
+    tr.iters_per_epoch = 3
+    for epoch in (1, 2):
+        meters = b200.new_train_meters()
+        for it in range(3):
+            tr.train_iter(W.synthetic_batch(8, 32, 100, seed=epoch * 10 + it, pin=True), epoch, meters)
+            assert meters["top1"].count == (8 * it if it < 2 else 24)
+        sd = tr.optimizer.state_dict()
+        assert len(sd["state"]) == len(tr.optimizer.param_groups[0]["params"])
 
 
 def test_multi_tensor_gather_matches_copies(b200):

@@ -24,7 +24,10 @@ def _loss_ok(got: float, G, name: str, key: str, scale: float = 1.0) -> bool:
     (KD) / 4.3e-5 (DKD) away from its fp64 run; measured on B200 the kernel is at 1.6e-5 / 1.3e-6
     there.  For such cases the bound is twice the reference's fp32-vs-fp64 distance instead."""
     r64, r32 = scale * float(G[f"{name}/{key}64"]), scale * float(G[f"{name}/{key}32"])
-    return abs(got - r64) <= max(TOL * abs(r64), 2.0 * abs(r32 - r64))
+    bound = TOL * abs(r64)
+    if name == "edge_1x2":          # the ONE named ill-conditioned case; every other case is held to rel 1e-5
+        bound = max(bound, 2.0 * abs(r32 - r64))
+    return abs(got - r64) <= bound
 
 
 @pytest.fixture(scope="module")
@@ -74,7 +77,8 @@ def test_loss_and_gradient_match_reference_fixture(case, loss_golden, ops):
         assert _loss_ok(lp2[1].item(), G, case.name, "ce", 0.5)
 
 
-@pytest.mark.parametrize("shape", [(64, 100), (256, 1000), (100, 40), (17, 512), (9, 2048), (6, 333), (5, 5000)])
+@pytest.mark.parametrize("shape", [(64, 100), (256, 1000), (100, 40), (17, 512), (9, 2048), (6, 333), (5, 5000),
+                                   (50, 116), (33, 120), (40, 128), (300, 112), (2500, 100), (70, 1024)])
 @pytest.mark.parametrize("T", [1.0, 4.0])
 def test_against_live_oracle_on_fresh_seeds(shape, T, ops):
     """Seeds that are in no fixture; oracle = fp64 closed forms (pinned to the reference on CPU)."""
@@ -94,6 +98,24 @@ def test_against_live_oracle_on_fresh_seeds(shape, T, ops):
     lp, gk, gc = ops.distill_loss(zs, zt, y, kind=ops.LOSS_KD, temperature=T, ce_mode=ops.CE_SPLIT)
     assert abs(lp[0].item() - l_kd) <= TOL * abs(l_kd) and abs(lp[1].item() - l_ce) <= TOL * abs(l_ce)
     assert oracle.max_rel_err(gk, g_kd) <= TOL and oracle.max_rel_err(gc, g_ce) <= TOL
+
+
+@pytest.mark.parametrize("shape", [(9, 101), (33, 37), (64, 100), (12, 10), (5, 81)])
+def test_kd_loss_without_targets(shape, ops):
+    """kd_loss(logits_student, logits_teacher, T) has no labels (KD.py:8-13): target=None must work on every
+    kernel path, including the one-row-per-block kernel that odd class counts take."""
+    import mdistiller_ddp_b200 as b200
+    B, C = shape
+    g = torch.Generator().manual_seed(B * 131 + C)
+    zs, zt = torch.randn(B, C, generator=g) * 3, torch.randn(B, C, generator=g) * 3
+    l_ref, g_ref = oracle.kd_closed_form(zs.numpy(), zt.numpy(), 4.0)
+    lp, gk, _ = ops.distill_loss(zs.cuda(), zt.cuda(), None, kind=ops.LOSS_KD, temperature=4.0)
+    assert abs(lp[0].item() - l_ref) <= TOL * abs(l_ref) and oracle.max_rel_err(gk, g_ref) <= TOL
+    a = zs.cuda().requires_grad_(True)
+    b200.kd_loss(a, zt.cuda(), 4.0).backward()
+    assert oracle.max_rel_err(a.grad, g_ref) <= TOL
+    with pytest.raises(RuntimeError, match="invalid argument"):       # DKD and CE do need labels
+        ops.distill_loss(zs.cuda(), zt.cuda(), None, kind=ops.LOSS_DKD)
 
 
 def test_strided_rows_and_unaligned_views(ops):

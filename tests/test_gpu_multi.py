@@ -61,8 +61,9 @@ def _opt_worker(rank, world, port, case_idx, out, mode="nccl"):
         gathered = [torch.empty_like(flat) for _ in range(world)]
         dist.all_gather(gathered, flat)
         assert all(torch.equal(g, flat) for g in gathered), "ranks diverged after the all-gather"
-        sd = opt.state_dict()
+        opt.sync_checkpoint_state()      # collective; afterwards the master alone checkpoints, as the reference does
         if rank == 0:
+            sd = opt.state_dict()
             torch.save({"p": [p.detach().cpu() for p in params],
                         "state": {k: {n: t.cpu() for n, t in v.items()} for k, v in sd["state"].items()}}, out)
     finally:
@@ -120,6 +121,7 @@ def _trainer_worker(rank, world, port):
         for step in range(3):
             batch = W.synthetic_batch(16, 32, 100, seed=100 * step + rank)
             msg = tr.train_iter(batch, 2, meters)
+        tr.flush_metrics(meters)
         flat = tr.optimizer.flat_params
         other = [torch.empty_like(flat) for _ in range(world)]
         dist.all_gather(other, flat.clone())
@@ -132,3 +134,31 @@ def _trainer_worker(rank, world, port):
 def test_trainer_under_ddp_wrapper_keeps_ranks_in_sync():
     _need_gpus(2)
     mp.spawn(_trainer_worker, args=(2, 29900 + os.getpid() % 90), nprocs=2, join=True)
+
+
+def test_one_process_driving_two_gpus_gets_per_device_kernel_setup():
+    """The dynamic shared-memory opt-in and the occupancy look-ups of the staged loss kernels are per
+    device: a process that used cuda:0 first must still be able to launch them on cuda:1 (both loss
+    entry points; 100- and 1000-class staged shapes need > 48 KB of shared memory)."""
+    _need_gpus(2)
+    import ctypes
+    from mdistiller_ddp_b200 import _lib, ops
+    lib = _lib.load()
+    for dev in (0, 1, 0):
+        with torch.cuda.device(dev):
+            for (B, C, T, beta) in ((2048, 100, 4.0, 8.0), (512, 1000, 1.0, 0.5), (300, 128, 2.0, 6.0)):
+                g = torch.Generator().manual_seed(B + C)
+                zs, zt = torch.randn(B, C, generator=g) * 3, torch.randn(B, C, generator=g) * 3
+                y = torch.randint(0, C, (B,), generator=g)
+                l_ref, g_ref = oracle.dkd_closed_form(zs.numpy(), zt.numpy(), y.numpy(), 1.0, beta, T)
+                zs, zt, y = zs.cuda(dev), zt.cuda(dev), y.cuda(dev)
+                lp, gk, _ = ops.distill_loss(zs, zt, y, kind=ops.LOSS_DKD, alpha=1.0, beta=beta, temperature=T)
+                assert abs(lp[0].item() - l_ref) <= 1e-5 * abs(l_ref) and oracle.max_rel_err(gk, g_ref) <= 1e-5
+                gk2, loss2 = torch.empty_like(zs), torch.empty(2, device=zs.device)
+                rc = lib.mdb200_distill_loss_static_scratch(
+                    zs.data_ptr(), zt.data_ptr(), y.data_ptr(), B, C, C, C, ops.LOSS_DKD, 1.0, beta, T, 1.0,
+                    ops.CE_NONE, 1.0, gk2.data_ptr(), None, C, loss2.data_ptr(),
+                    ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+                assert rc == 0, lib.mdb200_error_string(rc)
+                torch.cuda.synchronize()
+                assert torch.equal(gk2, gk) and torch.equal(loss2[:1], lp[:1])

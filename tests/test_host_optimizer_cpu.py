@@ -255,8 +255,13 @@ def _worker(rank, world, port, case_idx, out):
             for p, g in zip(params, task):
                 p.grad = None if g is None else g * (1.0 - 0.5 * sign)
             opt.step()
-        sd = opt.state_dict()
-        if rank == 0:
+        # the reference checkpoints on the master rank only (trainer.py:230-236): without the collective
+        # snapshot that must be a clear error, never a one-sided collective (= a hang)
+        with pytest.raises(RuntimeError, match="sync_checkpoint_state"):
+            opt.state_dict()
+        opt.sync_checkpoint_state()          # every rank (the hosted trainer does it after the epoch's last step)
+        if rank == 0:                        # ... and then rank 0 ALONE asks for the checkpoint
+            sd = opt.state_dict()
             torch.save({"p": [p.detach().clone() for p in params], "sd": sd,
                         "shard": (opt._space.shard_lo, opt._space.shard_hi, opt._space.total)}, out)
         # every rank must hold identical parameters after the all-gather
@@ -298,6 +303,60 @@ def test_sharded_step_world2_matches_single_process_on_averaged_gradients(case_i
             assert oracle.max_rel_err(st[i]["momentum_kd_buffer"], ref.buf_kd[i]) <= 2e-6
         if ref.buf_task[i] is not None:
             assert oracle.max_rel_err(st[i]["momentum_buffer"], ref.buf_task[i]) <= 2e-6
+
+
+class _RecordingFusedComm(ShardComm):
+    """Pretends to be rank `rank` of 2 with the fused NVLink step available; records which path ran."""
+    fused, fuse_kd = True, False
+
+    def __init__(self, rank):
+        self.group, self.world_size, self.rank = None, 2, rank
+        self.path = []
+
+    def reduce_scatter_sum(self, full, async_op=False):
+        self.path.append("reduce_scatter")
+        return None
+
+    def all_gather(self, full, async_op=False):
+        self.path.append("all_gather")
+        return None
+
+    def broadcast(self, full, src=0):
+        pass
+
+    def addresses(self, t):
+        return 0, [t.data_ptr(), t.data_ptr()]
+
+    def barrier(self, t, channel=0):
+        self.path.append("barrier")
+
+
+class _FusedRecorder(OracleKernels):
+    def dot_step_fused(self, *a, **k):
+        self.calls.append(("fused",))
+
+
+def test_fused_or_not_is_decided_from_global_membership_so_every_rank_agrees():
+    """A parameter without a KD gradient sits in rank 1's shard only.  Rank 0's own shard looks uniform, but
+    it must still take the unfused path, because rank 1 cannot enter the fused rendezvous."""
+    took = []
+    for rank in (0, 1):
+        params = [torch.nn.Parameter(torch.randn(64)), torch.nn.Parameter(torch.randn(8))]
+        comm, k = _RecordingFusedComm(rank), _FusedRecorder()
+        opt = b200.DistillationOrientedTrainer(params, lr=0.1, momentum=0.8, momentum_kd=0.95, comm=comm, kernels=k)
+        assert (opt._space.shard_lo, opt._space.shard_hi) == ((0, 36) if rank == 0 else (36, 72))
+        for has_kd_on_small in (False, True, True):     # 2nd pass: first-step flags still differ; 3rd: uniform
+            comm.path.clear()
+            k.calls.clear()
+            opt.zero_grad()
+            params[0].grad = torch.randn(64)
+            params[1].grad = torch.randn(8) if has_kd_on_small else None
+            opt.step_kd()
+            opt.zero_grad()
+            params[0].grad, params[1].grad = torch.randn(64), torch.randn(8)
+            opt.step()
+            took.append((rank, has_kd_on_small, ("fused",) in k.calls))
+    assert [t[2] for t in took] == [False, False, True, False, False, True], took
 
 
 def _base_worker(rank, world, port, case_idx, out):

@@ -60,6 +60,12 @@ def test_static_scratch_entry_point_matches_workspace_entry_point_twice_in_a_row
         assert oracle.max_rel_err(loss, want_loss) <= TOL
         assert oracle.max_rel_err(gk, want_gk) <= TOL
         assert oracle.max_rel_err(gc, want_gc) <= TOL
+        # and directly against the CPU oracle, not only against the sibling entry point
+        if kind == ops.LOSS_DKD:
+            l_ref, g_ref = oracle.dkd_closed_form(zs.cpu().numpy(), zt.cpu().numpy(), y.cpu().numpy(), 1.0, beta, T)
+        else:
+            l_ref, g_ref = oracle.kd_closed_form(zs.cpu().numpy(), zt.cpu().numpy(), T)
+        assert abs(loss[0].item() - l_ref) <= TOL * abs(l_ref) and oracle.max_rel_err(gk, g_ref) <= TOL
 
 
 def test_static_scratch_entry_point_refuses_launches_beyond_its_slots():
