@@ -13,8 +13,12 @@ Contract (one JSON line on rank 0):
   roofline  the DOT update kernel timed live inside the timed region (CUDA events on its stream),
           algorithmic bytes 32*N_shard per launch vs the measured HBM copy peak.
   kernels   isolated large-shape sweep of both kernels (L2 flushed between launches).
-  cpu_baseline  the CPU port of the reference path (oracle/) on a bounded sample, host cores.
-`--impl reference` prints the CPU arm alone (rank 0; other ranks exit 0).
+  cpu_baseline  the reference's own path on the host cores, bounded sample of the same config: the reference's
+          distiller / optimizer classes and backbones from the staged tree (oracle/make_ref.sh; kind "reference"),
+          or the oracle restatement when none is staged (kind "port").
+  dp_parity  (N > 1) the shipped data-parallel step against the oracle on rank-averaged gradients, before the
+          timed region; the run exits non-zero above rel 1e-5.
+`--impl reference` prints the CPU arm alone (rank 0; other ranks exit 0), same workload, batch, steps and warm-up.
 """
 
 from __future__ import annotations
@@ -59,12 +63,15 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="imagenet_r34_r18_dkd_dot")
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (0 = the workload's)")
-    ap.add_argument("--cpu-batch", type=int, default=16, help="bounded CPU sample: images per CPU step")
-    ap.add_argument("--comm", default="auto",
+    ap.add_argument("--cpu-batch", type=int, default=0,
+                    help="images per CPU step of the reference arm (0 = the workload's per-GPU batch, i.e. the same config)")
+    ap.add_argument("--comm", default=None,
                     choices=["auto", "nccl", "fused", "fused_kd", "fused_p2p", "fused_kd_p2p"],
-                    help="data-parallel step (N > 1): NCCL launches or the fused NVLink kernel; auto = fused "
-                         "(peer access at N <= 4, NVSwitch multicast with both buckets in the kernel above), "
-                         "NCCL launches if symmetric memory cannot be set up")
+                    help="data-parallel step (N > 1); default = whatever the package ships with "
+                         "(TailStepMixin.comm_mode, normally 'auto': trainer.resolve_comm_mode, NCCL launches if "
+                         "NVLink symmetric memory cannot be set up)")
+    ap.add_argument("--sweep", default="grid", choices=["grid", "short"],
+                    help="kernel sweep: the full SURVEY 8(d) grid or the eight headline shapes")
     ap.add_argument("--no-sweep", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     return ap.parse_args()
@@ -91,17 +98,50 @@ def profiled_traffic(kernel: str, n_elements: int):
 
 # ------------------------------------------------------------------------------- CPU arm
 
-def cpu_arm(workload: str, batch: int, steps: int, warmup: int, device: str = "cpu"):
-    """The reference's per-step path restated with torch ops (oracle/): backbones forward, dkd/kd + CE loss,
-    two backwards, per-tensor DOT loop -- the same sequence as DOT.train_iter (trainer.py:412-432).
-    device="cpu" is the CPU baseline / --impl reference arm; a CUDA device gives the "reference's torch
-    formulation on the same GPU" comparator (never the product path)."""
+def _reference_step(workload: str, batch: int, device: str):
+    """The reference's OWN objects on its OWN backbones (staged tree, see oracle/make_ref.sh): `DKD` / `KD`
+    distiller (distillers/DKD.py:54-84, KD.py:16-39), `DistillationOrientedTrainer` (engine/dot.py:58) or
+    `optim.SGD` (trainer.py:86-91), driven in the order of DOT.train_iter (trainer.py:412-444) /
+    BaseTrainer.train_iter (:257-321) -- minus their hard-coded `.cuda()` calls, which is why the trainer classes
+    themselves cannot run on the host."""
+    from oracle import ref_loader
+    from mdistiller_ddp_b200 import workloads as W
+    DKD, KD = ref_loader.distiller_classes()
+    teacher, student, hw, classes = W.build_pair(workload, seed=0, reference="require")
+    cfg = W.default_cfg(workload)
+    distiller = (DKD if cfg.DISTILLER.TYPE == "DKD" else KD)(student, teacher, cfg).to(device).train()
+    params = distiller.get_learnable_parameters()
+    m, d = cfg.SOLVER.SGD.MOMENTUM, cfg.SOLVER.DOT.DELTA
+    dot = cfg.SOLVER.TRAINER == "dot"
+    if dot:
+        opt = ref_loader.dot_module().DistillationOrientedTrainer(params, lr=cfg.SOLVER.LR, momentum=m - d,
+                                                                  momentum_kd=m + d, weight_decay=cfg.SOLVER.WEIGHT_DECAY)
+    else:
+        opt = torch.optim.SGD(params, lr=cfg.SOLVER.LR, momentum=m, weight_decay=cfg.SOLVER.WEIGHT_DECAY)
+    image, target, _ = W.synthetic_batch(batch, hw, classes, seed=1234, device=device)
+
+    def step():
+        preds, losses = distiller(image=image, target=target, epoch=1)
+        if dot:
+            opt.zero_grad(set_to_none=True)
+            losses["loss_kd"].backward(retain_graph=True)
+            opt.step_kd()
+            opt.zero_grad(set_to_none=True)
+            losses["loss_ce"].backward()
+            opt.step()
+        else:
+            opt.zero_grad()
+            sum(l.mean() for l in losses.values()).backward()
+            opt.step()
+        return sum(float(v.detach()) for v in losses.values())     # the reference reads its losses back every iteration too
+    return step, hw
+
+
+def _port_step(workload: str, batch: int, device: str):
+    """Fallback when no reference tree is staged: the oracle's restatement of the same sequence on stand-in nets."""
     import oracle
     from mdistiller_ddp_b200 import workloads as W
-
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    teacher, student, hw, classes = W.build_pair(workload, seed=0)
+    teacher, student, hw, classes = W.build_pair(workload, seed=0, reference="never")
     teacher.to(device).eval()
     student.to(device).train()
     cfg = W.default_cfg(workload)
@@ -113,7 +153,6 @@ def cpu_arm(workload: str, batch: int, steps: int, warmup: int, device: str = "c
     base_trainer = cfg.SOLVER.TRAINER == "base"
     sgd = torch.optim.SGD(params, lr=cfg.SOLVER.LR, momentum=m, weight_decay=cfg.SOLVER.WEIGHT_DECAY)
     image, target, _ = W.synthetic_batch(batch, hw, classes, seed=1234, device=device)
-    on_gpu = str(device) != "cpu"
 
     def step():
         zs, _ = student(image)
@@ -125,17 +164,34 @@ def cpu_arm(workload: str, batch: int, steps: int, warmup: int, device: str = "c
         else:
             l_ce = cfg.KD.LOSS.CE_WEIGHT * oracle.ce_loss(zs, target)
             l_kd = cfg.KD.LOSS.KD_WEIGHT * oracle.kd_loss(zs, zt, cfg.KD.TEMPERATURE)
-        if base_trainer:        # BaseTrainer.train_iter (trainer.py:257-321): summed loss, one backward, optim.SGD
+        if base_trainer:
             sgd.zero_grad()
             (l_kd + l_ce).backward()
             sgd.step()
-        else:                   # DOT.train_iter (trainer.py:412-432)
+        else:
             g_kd = torch.autograd.grad(l_kd, params, retain_graph=True)
             opt.step_kd(list(g_kd))
             g_ce = torch.autograd.grad(l_ce, params)
             opt.step(list(g_ce))
-        return l_kd.item() + l_ce.item()      # the reference reads its losses back every iteration too
+        return l_kd.item() + l_ce.item()
+    return step, hw
 
+
+def cpu_arm(workload: str, batch: int, steps: int, warmup: int, device: str = "cpu"):
+    """The reference's per-step path -- backbones forward, dkd/kd + CE loss, two backwards, per-tensor DOT loop --
+    timed on `device`.  device="cpu" is the CPU baseline / --impl reference arm on all host cores; a CUDA device
+    gives the "reference's torch code on the same GPU" comparator (never the product path).  kind "reference" =
+    the reference's own classes from the staged tree; "port" = the oracle restatement when none is staged."""
+    from mdistiller_ddp_b200 import refhost
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    if refhost.available():
+        step, hw = _reference_step(workload, batch, device)
+        kind, what = "reference", "the reference's own distiller / optimizer classes and backbones (staged tree)"
+    else:
+        step, hw = _port_step(workload, batch, device)
+        kind, what = "port", "oracle restatement on stand-in nets (no reference tree staged)"
+    on_gpu = str(device) != "cpu"
     for _ in range(warmup):
         step()
     if on_gpu:
@@ -146,9 +202,9 @@ def cpu_arm(workload: str, batch: int, steps: int, warmup: int, device: str = "c
     if on_gpu:
         torch.cuda.synchronize()
     dt = time.perf_counter() - t0
-    return {"value": batch * steps / dt, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{steps} steps x {batch} images of {workload} (same nets, {hw}x{hw} fp32) on the host CPU, "
-                      f"torch {torch.__version__} intra-op threads={cores}",
+    return {"value": batch * steps / dt, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": f"{steps} steps x {batch} images of {workload} ({hw}x{hw} fp32; {what}) on "
+                      f"{'the host CPU' if not on_gpu else device}, torch {torch.__version__} intra-op threads={cores}",
             "ms_per_step": 1e3 * dt / steps}
 
 
@@ -156,14 +212,16 @@ def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps, warmup = max(1, min(args.steps, 20)), max(1, min(args.warmup, 3))
-    r = cpu_arm(args.workload, args.cpu_batch, steps, warmup)
+    from mdistiller_ddp_b200 import workloads as W
+    steps, warmup = max(1, args.steps), max(0, args.warmup)        # exactly what was asked for, like our arm
+    batch = args.cpu_batch or args.batch or W.WORKLOADS[args.workload][7]
+    r = cpu_arm(args.workload, batch, steps, warmup)
     line = {
         "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": steps, "warmup": warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_label(args.workload), "per_step_images": args.cpu_batch,
-                   "device": "host CPU (oracle port of the reference path: same nets, per-tensor DOT loop)"},
+        "config": {"workload": workload_label(args.workload), "per_gpu_batch": batch, "per_step_images": batch,
+                   "device": "host CPU, all cores; " + r["sample"]},
         "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -214,8 +272,9 @@ class ClockSampler:
 
 # ------------------------------------------------------------------------------- GPU arm
 
-def kernel_sweep(dev):
-    """Both kernels alone at BASELINE.json's sweep sizes; L2 flushed between launches (see `timed`)."""
+def kernel_sweep(dev, grid=True):
+    """Both kernels alone at BASELINE.json's sweep sizes; L2 flushed between launches (see `timed`).  Shapes below
+    a few MB are launch-latency bound: read their `us` (one launch each), not their GB/s."""
     from mdistiller_ddp_b200 import ops
     peak, _ = hbm_peak()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -238,25 +297,44 @@ def kernel_sweep(dev):
                 ts.append(a.elapsed_time(b) * 1e-3)
         return statistics.median(ts), min(ts)
 
-    for (B, C, kind, T, beta, ce, tag) in (
-            (65536, 1000, ops.LOSS_DKD, 1.0, 0.5, ops.CE_NONE, "dkd_65536x1000"),
-            (65536, 1000, ops.LOSS_DKD, 1.0, 0.5, ops.CE_SPLIT, "dkd+ce_split_65536x1000"),
-            (65536, 1000, ops.LOSS_KD, 1.0, 1.0, ops.CE_NONE, "kd_65536x1000"),
-            (16384, 1000, ops.LOSS_DKD, 1.0, 0.5, ops.CE_NONE, "dkd_16384x1000"),
-            (65536, 100, ops.LOSS_DKD, 4.0, 8.0, ops.CE_NONE, "dkd_65536x100"),
-            (65536, 100, ops.LOSS_DKD, 4.0, 8.0, ops.CE_SPLIT, "dkd+ce_split_65536x100_T4"),
-            (256, 1000, ops.LOSS_DKD, 1.0, 0.5, ops.CE_SPLIT, "dkd+ce_split_256x1000"),
-            (64, 100, ops.LOSS_DKD, 4.0, 8.0, ops.CE_SPLIT, "dkd+ce_split_64x100_T4")):
-        zs = torch.randn(B, C, device=dev) * 3
-        zt = torch.randn(B, C, device=dev) * 3
-        y = torch.randint(0, C, (B,), device=dev)
-        gk, gc, lo = torch.empty_like(zs), torch.empty_like(zs), torch.empty(2, device=dev)
+    head = [
+        (65536, 1000, ops.LOSS_DKD, 1.0, 0.5, ops.CE_NONE, "dkd_65536x1000"),
+        (65536, 1000, ops.LOSS_DKD, 1.0, 0.5, ops.CE_SPLIT, "dkd+ce_split_65536x1000"),
+        (65536, 1000, ops.LOSS_KD, 1.0, 1.0, ops.CE_NONE, "kd_65536x1000"),
+        (16384, 1000, ops.LOSS_DKD, 1.0, 0.5, ops.CE_NONE, "dkd_16384x1000"),
+        (65536, 100, ops.LOSS_DKD, 4.0, 8.0, ops.CE_NONE, "dkd_65536x100"),
+        (65536, 100, ops.LOSS_DKD, 4.0, 8.0, ops.CE_SPLIT, "dkd+ce_split_65536x100_T4"),
+        (256, 1000, ops.LOSS_DKD, 1.0, 0.5, ops.CE_SPLIT, "dkd+ce_split_256x1000"),
+        (64, 100, ops.LOSS_DKD, 4.0, 8.0, ops.CE_SPLIT, "dkd+ce_split_64x100_T4")]
+    shapes = list(head)
+    if grid:
+        # B in {64 ... 65536} x C in {100, 1000}; DKD hyper-sets (alpha, beta, T) = (1,8,4), (1,6,4),
+        # (1,0.5,1); KD at T in {4, 1}.  Tags: <kind>_<B>x<C>_b<beta>_T<T>.
+        seen = {(B, C, k, T, be, ce) for (B, C, k, T, be, ce, _) in head}
+        for C in (100, 1000):
+            for B in (64, 256, 1024, 4096, 16384, 65536):
+                for (beta, T) in ((8.0, 4.0), (6.0, 4.0), (0.5, 1.0)):
+                    if (B, C, ops.LOSS_DKD, T, beta, ops.CE_NONE) not in seen:
+                        shapes.append((B, C, ops.LOSS_DKD, T, beta, ops.CE_NONE, f"grid_dkd_{B}x{C}_b{beta:g}_T{T:g}"))
+                for T in (4.0, 1.0):
+                    if (B, C, ops.LOSS_KD, T, 1.0, ops.CE_NONE) not in seen:
+                        shapes.append((B, C, ops.LOSS_KD, T, 1.0, ops.CE_NONE, f"grid_kd_{B}x{C}_T{T:g}"))
+    bufs = {}
+    for (B, C, kind, T, beta, ce, tag) in shapes:
+        if (B, C) not in bufs:
+            bufs.clear()
+            g = torch.Generator(device=dev).manual_seed(0)
+            bufs[(B, C)] = (torch.randn(B, C, device=dev, generator=g) * 3, torch.randn(B, C, device=dev, generator=g) * 3,
+                            torch.randint(0, C, (B,), device=dev, generator=g),
+                            torch.empty(B, C, device=dev), torch.empty(B, C, device=dev), torch.empty(2, device=dev))
+        zs, zt, y, gk, gc, lo = bufs[(B, C)]
         med, best = timed(lambda: ops.distill_loss(zs, zt, y, kind=kind, alpha=1.0, beta=beta, temperature=T,
-                                                   ce_mode=ce, grad_kd=gk, grad_ce=gc, loss_out=lo))
+                                                   ce_mode=ce, grad_kd=gk, grad_ce=gc, loss_out=lo),
+                          reps=10 if not tag.startswith("grid_") else 6)
         nbytes = (16 if ce == ops.CE_SPLIT else 12) * B * C + 8 * B + 8
         out[tag] = {"us": med * 1e6, "GB/s": nbytes / med / 1e9, "frac_of_measured_peak": nbytes / med / 1e9 / peak,
-                    "frac_of_8TBs": nbytes / med / 8e12, "bytes": nbytes}
-        del zs, zt, gk, gc
+                    "frac_of_8TBs": nbytes / med / 8e12, "bytes": nbytes, "launches": 1}
+    bufs.clear()
     for n, tag in ((11_689_512, "dot_resnet18_11.7M"), (25_557_032, "dot_resnet50_25.6M")):
         p, gt, gk2 = (torch.randn(n, device=dev) * 0.1 for _ in range(3))
         vt, vk = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
@@ -281,7 +359,17 @@ def torch_on_gpu_baseline(dev, workload=None, batch=0):
     on CUDA tensors.  A baseline leg like cpu_baseline: never part of the product path."""
     import oracle
     import torchvision.models as tvm
+    from mdistiller_ddp_b200 import refhost
     out = {}
+    if refhost.available():            # the reference's own functions (staged tree) ...
+        from oracle import ref_loader
+        ref_dkd, _ = ref_loader.loss_functions()
+        RefDot = ref_loader.dot_module().DistillationOrientedTrainer
+        out["source"] = "reference functions (dkd_loss DKD.py:8, F.cross_entropy, DistillationOrientedTrainer dot.py:58)"
+    else:                              # ... or the oracle's restatement of them
+        ref_dkd, RefDot = oracle.dkd_loss, None
+        out["source"] = "oracle restatement (no reference tree staged)"
+    import torch.nn.functional as F
 
     def timed(fn, reps=5):
         fn()
@@ -303,18 +391,30 @@ def torch_on_gpu_baseline(dev, workload=None, batch=0):
 
         def ref_loss():
             zs.grad = None
-            (oracle.dkd_loss(zs, zt, y, 1.0, beta, T) + oracle.ce_loss(zs, y)).backward()
+            (ref_dkd(zs, zt, y, 1.0, beta, T) + F.cross_entropy(zs, y)).backward()
         t = timed(ref_loss)
         out[f"torch_dkd+ce_fwd_bwd_{B}x{C}"] = {"us": t * 1e6, "algorithmic_GB/s": (12 * B * C) / t / 1e9}
         del zs, zt
     params = [p.detach().clone().to(dev) for p in tvm.resnet18(weights=None).parameters()]
-    opt = oracle.DotListOracle(params, lr=0.2, momentum=0.81, momentum_kd=0.99, weight_decay=1e-4)
     g1 = [torch.randn_like(p) * 0.1 for p in params]
     g2 = [torch.randn_like(p) * 0.1 for p in params]
+    if RefDot is not None:
+        params = [p.requires_grad_(True) for p in params]
+        opt = RefDot(params, lr=0.2, momentum=0.81, momentum_kd=0.99, weight_decay=1e-4)
 
-    def ref_dot():
-        opt.step_kd(g1)
-        opt.step(g2)
+        def ref_dot():
+            for p, g in zip(params, g1):
+                p.grad = g
+            opt.step_kd()
+            for p, g in zip(params, g2):
+                p.grad = g
+            opt.step()
+    else:
+        opt = oracle.DotListOracle(params, lr=0.2, momentum=0.81, momentum_kd=0.99, weight_decay=1e-4)
+
+        def ref_dot():
+            opt.step_kd(g1)
+            opt.step(g2)
     t = timed(ref_dot, reps=10)
     n = sum(p.numel() for p in params)
     out["torch_dot_step_resnet18_62_tensors"] = {"us": t * 1e6, "algorithmic_GB/s": 32 * n / t / 1e9}
@@ -323,9 +423,90 @@ def torch_on_gpu_baseline(dev, workload=None, batch=0):
     if workload is not None:
         r = cpu_arm(workload, batch, steps=10, warmup=5, device=dev)
         out["torch_train_step"] = {"images/s": r["value"], "ms_per_step": r["ms_per_step"], "per_gpu_batch": batch,
-                                   "what": "oracle losses + autograd + per-tensor DOT loop on CUDA tensors, losses read back "
-                                           "each step (as trainer.py:439-444 does)"}
+                                   "what": r["sample"] + "; losses read back each step (as trainer.py:439-444 does)"}
     return out
+
+
+def dp_parity(trainer_cls, kind, world, rank, dev):
+    """Numerics of the data-parallel step AS SHIPPED (same comm plumbing the timed trainer gets), N > 1: 12 steps of
+    tests/_cases.DOT_CASES[6] (a res8x4-like list of 32 tensors, 1.23 M elements) with per-rank-scaled gradients whose
+    mean over ranks is the single-process gradient, against the CPU oracle fed the rank-averaged gradients
+    (mdistiller/engine/dot.py:15-55,165-170 for DOT; torch.optim.SGD for the base trainer) --
+    parameters AND momenta (through sync_checkpoint_state + rank 0's state_dict).  All ranks must end bit-equal."""
+    import torch.distributed as dist
+    import oracle
+    import mdistiller_ddp_b200 as b200
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _cases
+    case = _cases.DOT_CASES[6]
+    host = trainer_cls.__new__(trainer_cls)            # only _make_comm is used: the package's own comm policy
+    host.trainer_kind = kind
+    comm = host._make_comm()
+    params = [torch.nn.Parameter((p.clone() + (0.5 if rank else 0.0)).to(dev)) for p in _cases.make_params(case)]
+    if kind == "dot":
+        opt = b200.DistillationOrientedTrainer(params, lr=case.lr, momentum=case.momentum - case.delta,
+                                               momentum_kd=case.momentum + case.delta, weight_decay=case.wd, comm=comm)
+    else:
+        opt = b200.FlatSGD(params, lr=case.lr, momentum=case.momentum, weight_decay=case.wd, comm=comm)
+    shapes = [p.shape for p in params]
+    f_kd = 1.0 + 0.25 * (rank - (world - 1) / 2)
+    f_task = 1.0 - 0.5 * (rank - (world - 1) / 2)
+    for step in range(12):
+        if step == 6:
+            opt.param_groups[0]["lr"] = case.lr * 0.1
+        kd, task = _cases.make_grads(case, step, shapes)
+        if kind == "dot":
+            opt.zero_grad()
+            for p, g in zip(params, kd):
+                p.grad = (g * f_kd).to(dev)
+            opt.step_kd()
+        opt.zero_grad()
+        for p, g in zip(params, task):
+            p.grad = (g * f_task).to(dev)
+        opt.step()
+    flat = opt.flat_params.clone()
+    gathered = [torch.empty_like(flat) for _ in range(world)]
+    dist.all_gather(gathered, flat)
+    bit_equal = all(torch.equal(g, flat) for g in gathered)
+    opt.sync_checkpoint_state()
+    worst = 0.0
+    if rank == 0:
+        sd = opt.state_dict()["state"]
+        ref_p = [p.clone() for p in _cases.make_params(case)]
+        if kind == "dot":
+            ref = oracle.DotListOracle(ref_p, lr=case.lr, momentum=case.momentum - case.delta,
+                                       momentum_kd=case.momentum + case.delta, weight_decay=case.wd)
+        else:
+            ref_p = [torch.nn.Parameter(p) for p in ref_p]
+            ref = torch.optim.SGD(ref_p, lr=case.lr, momentum=case.momentum, weight_decay=case.wd)
+        for step in range(12):
+            kd, task = _cases.make_grads(case, step, shapes)
+            if kind == "dot":
+                if step == 6:
+                    ref.hp["lr"] = case.lr * 0.1
+                ref.step_kd(kd)
+                ref.step(task)
+            else:
+                if step == 6:
+                    ref.param_groups[0]["lr"] = case.lr * 0.1
+                for p, g in zip(ref_p, task):
+                    p.grad = g.clone()
+                ref.step()
+        for i, (p, q) in enumerate(zip(params, ref_p)):
+            worst = max(worst, oracle.max_rel_err(p.detach().cpu(), q.detach()))
+            if kind == "dot":
+                worst = max(worst, oracle.max_rel_err(sd[i]["momentum_buffer"].cpu(), ref.buf_task[i]),
+                            oracle.max_rel_err(sd[i]["momentum_kd_buffer"].cpu(), ref.buf_kd[i]))
+            else:
+                worst = max(worst, oracle.max_rel_err(sd[i]["momentum_buffer"].cpu(), ref.state[q]["momentum_buffer"]))
+    t = torch.tensor([worst, 0.0 if bit_equal else 1.0], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    worst, diverged = t.tolist()
+    fused = getattr(opt, "last_fused", None)
+    del opt, params
+    return {"mode": host.comm_mode_used, "fused_step": fused, "max_rel_err": worst, "ranks_bit_equal": diverged == 0.0,
+            "steps": 12, "case": case.name, "tolerance": 1e-5,
+            "oracle": "single-process reference arithmetic on rank-averaged gradients (params + momenta)"}
 
 
 def run_b200_arm(args):
@@ -348,23 +529,21 @@ def run_b200_arm(args):
     teacher, student, hw, classes = W.build_pair(args.workload, seed=0)
     cfg = W.default_cfg(args.workload)
     distiller = b200.distiller_dict[cfg.DISTILLER.TYPE](student, teacher, cfg).to(dev).train()
-    comm_mode = args.comm
-    if comm_mode == "auto":
-        # measured on one HGX box (profiles/r1_bench_n*): peer loads win up to 4 GPUs, the in-switch
-        # (NVLS multicast) reduction of both buckets wins at 8
-        comm_mode = "nccl" if world == 1 else ("fused_p2p" if world <= 4 else "fused_kd")
+    if args.comm is not None:                  # otherwise: exactly what the package ships with
+        b200.TailStepMixin.comm_mode = args.comm
+    parity = None
+    if world > 1:
+        parity = dp_parity(b200.StandaloneTrainer, cfg.SOLVER.TRAINER, world, rank, dev)
+        if not (parity["max_rel_err"] <= 1e-5 and parity["ranks_bit_equal"]):
+            if rank == 0:
+                print(json.dumps({"dp_parity": parity, "error": "data-parallel step disagrees with the oracle"}), flush=True)
+            dist.destroy_process_group()
+            raise SystemExit(3)
+    trainer = b200.StandaloneTrainer(distiller, cfg)
+    args.comm = trainer.comm_mode_used
     comm_note = ""
-    b200.TailStepMixin.comm_mode = comm_mode
-    try:
-        trainer = b200.StandaloneTrainer(distiller, cfg)
-    except Exception as e:                      # symmetric memory / multicast not available on this box
-        if comm_mode == "nccl" or args.comm != "auto":
-            raise
-        comm_note = f" (fused step unavailable: {type(e).__name__}: {str(e)[:120]}; using NCCL launches)"
-        comm_mode = "nccl"
-        b200.TailStepMixin.comm_mode = comm_mode
-        trainer = b200.StandaloneTrainer(distiller, cfg)
-    args.comm = comm_mode
+    if getattr(trainer, "comm_fallback_reason", None):
+        comm_note = f" (fused step unavailable: {trainer.comm_fallback_reason}; using NCCL launches)"
     n_params = sum(p.numel() for p in distiller.get_learnable_parameters())
     shard_elems = trainer.optimizer._space.shard_len
 
@@ -429,11 +608,10 @@ def run_b200_arm(args):
     clocks = sampler.summary(t_wall0, t_wall1)
 
     # end-to-end: public call with host (pinned) batch, H2D + metrics D2H inside the timed region
-    # (metrics_lag = 1: the loss/top-k read-back of step i is awaited during step i+1, which lets the
-    #  H2D copy of the next batch overlap the current step; every step's result is still read inside
-    #  the timed region, the last one by flush_metrics)
+    # (the trainer's default metrics_lag = 1: the loss/top-k read-back of step i is awaited during step i+1,
+    #  which lets the H2D copy of the next batch overlap the current step; every step's result is still read
+    #  inside the timed region, the last one by flush_metrics)
     meters = b200.new_train_meters()
-    trainer.metrics_lag = 1
     for _ in range(2):
         trainer.train_iter(host, epoch, meters)
     trainer.flush_metrics(meters)
@@ -500,6 +678,8 @@ def run_b200_arm(args):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_label(args.workload),
                    "per_gpu_batch": per_gpu, "global_batch": per_gpu * world, "student_params": n_params,
+                   "backbones": ("the reference's own modules (staged tree)" if W.backbone_source == "reference"
+                                 else "architecture-equivalent stand-ins (no reference tree staged)"),
                    "parallelism": (f"dp{world}: reduce-scatter x2 -> DOT on 1/{world} shard -> all-gather (NCCL)" if args.comm == "nccl" or world == 1
                                    else f"dp{world}: fused NVLink kernel ({args.comm}): gradient sum over ranks -> DOT on 1/{world} shard -> parameters to every rank") + comm_note,
                    "backbone_math": "fp32 storage, cuDNN TF32 convolutions allowed (torch default, as the reference)",
@@ -507,24 +687,27 @@ def run_b200_arm(args):
         "e2e": {"value": world * per_gpu * args.steps / e2e_secs, "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 20, "ms_per_step": 1e3 * e2e_secs / args.steps,
                 "api": "StandaloneTrainer.train_iter((image, target, index), epoch, meters) -- the mirror of "
-                       "DOT.train_iter (trainer.py:412-461); metrics_lag=1, flushed inside the timed region"},
+                       f"DOT.train_iter (trainer.py:412-461); metrics_lag={trainer.metrics_lag} (the package default), flushed inside the timed region"},
         "gpu_launches": launches,
         "optimizer_step": {"us": 1e6 * sum(step_t) / max(1, len(step_t)),
                            "what": "optimizer.step(): task-bucket collective + DOT kernel + parameter write-back, "
                                    "CUDA events on the compute stream", "comm": args.comm if world > 1 else "none",
                            "fused": getattr(trainer.optimizer, "last_fused", None)},
         "clocks": clocks,
+        "dp_parity": parity,
         "roofline": roofline,
         "loss_kernel_in_step": {"kernel": "loss_rows_in_registers (mdb200_distill_loss)", "us_per_launch": loss_avg * 1e6,
                                 "bytes_per_launch": loss_bytes, "GB/s": loss_bytes / loss_avg / 1e9,
                                 "note": "256x1000 is 4 MB: launch-latency bound, see kernels{} for the large-shape sweep"},
     }
     if not args.no_sweep:
-        line["kernels"] = kernel_sweep(dev)
+        line["kernels"] = kernel_sweep(dev, grid=(args.sweep == "grid"))
         if world == 1:
             line["torch_on_b200_baseline"] = torch_on_gpu_baseline(dev, args.workload, per_gpu)
     if world == 1 and not args.no_cpu:
-        line["cpu_baseline"] = {k: v for k, v in cpu_arm(args.workload, args.cpu_batch, 8, 1).items()
+        # bounded sample of the SAME config (same per-step batch): about 10-30 s of host work
+        cpu_steps = 3 if args.workload.startswith("imagenet") else 20
+        line["cpu_baseline"] = {k: v for k, v in cpu_arm(args.workload, args.cpu_batch or per_gpu, cpu_steps, 1).items()
                                 if k != "ms_per_step"}
     else:
         line["cpu_baseline"] = None

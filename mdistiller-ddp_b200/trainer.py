@@ -73,7 +73,7 @@ class TailStepMixin:
             return None
         world = dist.get_world_size()
         mode = resolve_comm_mode(self.comm_mode, world)
-        if mode != "nccl" and world > 1:
+        if mode != "nccl" and world > 1 and self.trainer_kind == "dot":
             try:
                 comm = SymmetricShardComm(fuse_kd=mode.startswith("fused_kd"), use_multicast=not mode.endswith("p2p"))
                 comm.probe()                    # allocation + rendezvous work on this box?

@@ -199,11 +199,30 @@ def default_cfg(workload: str = "imagenet_r34_r18_dkd_dot") -> SimpleNamespace:
     )
 
 
-def build_pair(workload: str, seed: int = 0):
+# registry names of the same architectures in the reference (models/cifar/__init__.py:32, models/imagenet/__init__.py)
+_REFERENCE_NAMES = {"vgg8": "vgg8", "vgg13": "vgg13"}
+
+backbone_source = "stand-in"      # what the last build_pair() built: "reference" | "stand-in"
+
+
+def build_pair(workload: str, seed: int = 0, reference: str = "auto"):
+    """(teacher, student, image size, classes), random-init.  ``reference="auto"``: the reference's OWN backbone
+    modules when a reference tree is available (``refhost.locate()``: mounted, or staged by oracle/make_ref.sh),
+    else the architecture-equivalent stand-ins above; "never" / "require" force one or the other."""
+    global backbone_source
     teacher_name, student_name, builder, hw, classes = WORKLOADS[workload][:5]
+    from . import refhost
+    use_ref = reference == "require" or (reference == "auto" and refhost.available())
     torch.manual_seed(seed)
-    teacher = builder(teacher_name, classes)
-    student = builder(student_name, classes)
+    if use_ref:
+        dataset = "imagenet" if workload.startswith("imagenet") else "cifar100"
+        teacher = refhost.backbone(_REFERENCE_NAMES.get(teacher_name, teacher_name), classes, dataset)
+        student = refhost.backbone(_REFERENCE_NAMES.get(student_name, student_name), classes, dataset)
+        backbone_source = "reference"
+    else:
+        teacher = builder(teacher_name, classes)
+        student = builder(student_name, classes)
+        backbone_source = "stand-in"
     return teacher, student, hw, classes
 
 

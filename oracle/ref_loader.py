@@ -1,10 +1,11 @@
-"""Import the *unmodified* reference in place (build container only).
+"""Import the *unmodified* reference: mounted tree here, staged archive on the GPU box.
 
-TEST INFRASTRUCTURE.  ``/root/reference`` does not exist on the GPU box, so
-nothing that runs there (``-m gpu`` tests, ``smoke()``, ``bench.py``) may call
-into this module; it exists to (a) generate the committed fixtures under
-``tests/golden/`` and (b) let CPU-only tests cross-check the oracle against the
-live reference when the tree happens to be mounted.
+TEST INFRASTRUCTURE.  ``/root/reference`` does not exist on the GPU box; what runs there
+reads the archive ``oracle/make_ref.sh`` staged under the git-ignored ``oracle/_ref/``
+(unpacked by ``mdistiller_ddp_b200.refhost``), never ``/root/reference``.  This module (a)
+generates the committed fixtures under ``tests/golden/``, (b) lets tests cross-check the
+oracle against the live reference, and (c) gives ``bench.py --impl reference`` the
+reference's own functions to time.
 
 Shims (no reference file is edited), following SURVEY.md section 0.1:
   D6  ``mdistiller/models/imagenet/vit.py`` needs timm and evaluates an
@@ -20,26 +21,23 @@ import importlib
 import importlib.util
 import os
 import sys
-import types
 
-REF_ROOT = os.environ.get("MDISTILLER_REF_ROOT", "/root/reference")
+import mdistiller_ddp_b200  # noqa: F401  (routes the hyphenated package directory)
+from mdistiller_ddp_b200 import refhost
 
 
 def available() -> bool:
-    return os.path.isfile(os.path.join(REF_ROOT, "mdistiller", "distillers", "DKD.py"))
+    return refhost.available()
 
 
 def _ensure_path() -> None:
-    if not available():
-        raise FileNotFoundError(f"reference tree not mounted at {REF_ROOT}")
-    if REF_ROOT not in sys.path:
-        sys.path.insert(0, REF_ROOT)
-    name = "mdistiller.models.imagenet.vit"
-    if name not in sys.modules:
-        stub = types.ModuleType(name)
-        for n in ("tiny", "small", "base", "large"):
-            setattr(stub, f"vit_{n}_patch16_224", None)
-        sys.modules[name] = stub
+    refhost.ensure_importable()
+
+
+def __getattr__(name):          # REF_ROOT: resolved lazily (mounted tree, or the staged archive unpacked)
+    if name == "REF_ROOT":
+        return refhost.locate()
+    raise AttributeError(name)
 
 
 def loss_functions():
@@ -66,7 +64,7 @@ def dot_module():
     key = "_ref_engine_dot"
     if key in sys.modules:
         return sys.modules[key]
-    path = os.path.join(REF_ROOT, "mdistiller", "engine", "dot.py")
+    path = os.path.join(refhost.locate(), "mdistiller", "engine", "dot.py")
     spec = importlib.util.spec_from_file_location(key, path)
     mod = importlib.util.module_from_spec(spec)
     sys.modules[key] = mod
@@ -76,18 +74,8 @@ def dot_module():
 
 def cifar_models():
     """cifar_model_dict with the D5 abstract-method shim applied."""
-    _ensure_path()
-    for sub, cls in (("resnet", "ResNet"), ("wrn", "WideResNet"),
-                     ("ShuffleNetv1", "ShuffleNet"), ("mobilenetv2", "MobileNetV2")):
-        m = importlib.import_module(f"mdistiller.models.cifar.{sub}")
-        getattr(m, cls).__abstractmethods__ = frozenset()
-    from mdistiller.models.cifar import cifar_model_dict  # type: ignore
-
-    return cifar_model_dict
+    return refhost.cifar_models()
 
 
 def imagenet_models():
-    _ensure_path()
-    from mdistiller.models.imagenet import imagenet_model_dict  # type: ignore
-
-    return imagenet_model_dict
+    return refhost.imagenet_models()
