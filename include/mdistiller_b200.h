@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define MDB200_ABI_VERSION 2
+#define MDB200_ABI_VERSION 3
 
 #if defined(__GNUC__)
 #define MDB200_API __attribute__((visibility("default")))
@@ -182,9 +182,18 @@ MDB200_API int mdb200_dot_step(float *p, const float *g_task, const float *g_kd,
  *                                         the second backward); only the task gradient is fetched
  *   v_task, v_kd                          rank-local momentum, shard_len elements
  *   grad_scale                            normally 1/world
- * shard_lo and shard_len are multiples of 4; world <= 16.  The caller must order the launch
- * after every rank's gradients are complete and visible (symmetric-memory barrier) and must
- * not let any rank read P before every rank's kernel has finished (second barrier).
+ *   sync_pads, rank, epoch                cross-rank ordering inside the kernel: host array[world] of every
+ *                                         rank's SYNC PAD (64 uint32 of symmetric memory, zero before the first
+ *                                         use; own rank included), this rank's index, and a launch counter that
+ *                                         starts at 1 and grows by 1 with every launch that uses the pads (the
+ *                                         same value on every rank).  The kernel then waits until every rank's
+ *                                         gradients are complete before its first fetch and does not finish
+ *                                         until every rank has written this rank's copy of P.  One rank per GPU;
+ *                                         a rank that never launches makes the others trap after 20 s.
+ *                                         sync_pads == NULL: no handshake -- the caller must order the launch
+ *                                         after every rank's gradients (a barrier before) and keep every rank
+ *                                         from reading P until all kernels have finished (a barrier after).
+ * shard_lo and shard_len are multiples of 4; world <= 16.
  */
 MDB200_API int mdb200_dot_step_fused(float *p_local, float *p_multicast, float *const *p_peers,
                     const float *g_task_local, const float *g_task_multicast, float *const *g_task_peers,
@@ -192,7 +201,23 @@ MDB200_API int mdb200_dot_step_fused(float *p_local, float *p_multicast, float *
                     int kd_is_reduced, float *v_task, float *v_kd,
                     int64_t shard_lo, int64_t shard_len, int world,
                     float lr, float momentum, float momentum_kd, float weight_decay,
-                    float dampening, float grad_scale, int first_task, int first_kd, void *stream);
+                    float dampening, float grad_scale, int first_task, int first_kd,
+                    uint32_t *const *sync_pads, int rank, uint32_t epoch, void *stream);
+
+/*
+ * The same fused data-parallel step for the base trainer's single gradient bucket: gradient sum over ranks ->
+ * momentum SGD (arithmetic of mdb200_sgd_step) on this rank's shard -> parameters written to every rank, one
+ * kernel over NVLink peer memory.
+ *
+ * Replaces DDP's bucketed all-reduce (tools/train.py:86) followed by optim.SGD.step()
+ * (mdistiller/engine/trainer.py:86-91, 321) and the NCCL reduce-scatter / all-gather pair of the unfused step.
+ * Arguments as in mdb200_dot_step_fused (one bucket `g`, one momentum shard `v`; v may be NULL when momentum == 0).
+ */
+MDB200_API int mdb200_sgd_step_fused(float *p_local, float *p_multicast, float *const *p_peers,
+                    const float *g_local, const float *g_multicast, float *const *g_peers, float *v,
+                    int64_t shard_lo, int64_t shard_len, int world,
+                    float lr, float momentum, float weight_decay, float dampening, float grad_scale,
+                    int first_step, uint32_t *const *sync_pads, int rank, uint32_t epoch, void *stream);
 
 /*
  * Multi-tensor gather: copy n_tensors per-parameter gradient tensors into one flat fp32 bucket in a

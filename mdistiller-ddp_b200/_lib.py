@@ -14,7 +14,7 @@ import threading
 from .build import LIB_PATH
 
 # constants mirrored from the header
-ABI_VERSION = 2
+ABI_VERSION = 3
 LOSS_DKD, LOSS_KD = 0, 1
 CE_NONE, CE_SPLIT, CE_COMBINED = 0, 1, 2
 DOT_BOTH, DOT_TASK_ONLY, DOT_KD_ONLY = 0, 1, 2
@@ -36,7 +36,10 @@ SIGNATURES = {
     "mdb200_dot_step": (_int, [_ptr, _ptr, _ptr, _ptr, _ptr, _i64, _f32, _f32, _f32, _f32, _f32, _f32,
                                _int, _int, _int, _ptr]),
     "mdb200_dot_step_fused": (_int, [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _int, _ptr, _ptr,
-                                     _i64, _i64, _int, _f32, _f32, _f32, _f32, _f32, _f32, _int, _int, _ptr]),
+                                     _i64, _i64, _int, _f32, _f32, _f32, _f32, _f32, _f32, _int, _int,
+                                     _ptr, _int, C.c_uint32, _ptr]),
+    "mdb200_sgd_step_fused": (_int, [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i64, _int, _f32, _f32, _f32, _f32,
+                                     _f32, _int, _ptr, _int, C.c_uint32, _ptr]),
     "mdb200_sgd_step": (_int, [_ptr, _ptr, _ptr, _i64, _f32, _f32, _f32, _f32, _f32, _ptr, _int, _ptr]),
     "mdb200_adam_step": (_int, [_ptr, _ptr, _ptr, _ptr, _i64, _f32, C.c_double, C.c_double, _f32, _f32, _int, _i64,
                                 _f32, _ptr, _ptr]),

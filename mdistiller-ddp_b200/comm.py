@@ -73,14 +73,37 @@ class SymmetricShardComm(ShardComm):
     fused = True
 
     def __init__(self, group: Optional[dist.ProcessGroup] = None, fuse_kd: bool = False,
-                 use_multicast: bool = True, barrier_timeout_ms: int = 20000):
+                 use_multicast: bool = True, barrier_timeout_ms: int = 20000, in_kernel_sync: bool = True):
         super().__init__(group)
         if self.world_size > 16:
             raise ValueError("the fused kernel addresses at most 16 peers")
         self.fuse_kd = fuse_kd
         self.use_multicast = use_multicast
         self.barrier_timeout_ms = barrier_timeout_ms
+        # True: the fused kernel orders itself against the other ranks through a sync pad in symmetric memory
+        # (no barrier launches around it); False: two symmetric-memory barrier launches bracket it
+        self.in_kernel_sync = in_kernel_sync
         self._handles = {}
+        self._pad = None
+        self._pad_ptrs = None
+        self._epoch = 0
+
+    def next_sync(self):
+        """(pad address on every rank, this rank, epoch) for the next fused launch -- every rank must call this
+        the same number of times -- or None when the launch is bracketed by barrier launches instead."""
+        if not self.in_kernel_sync:
+            return None
+        if self._pad is None:
+            import torch.distributed._symmetric_memory as symm_mem
+            dev = torch.device("cuda", torch.cuda.current_device())
+            self._pad = symm_mem.empty(64, dtype=torch.int32, device=dev)
+            hdl = symm_mem.rendezvous(self._pad, self.group if self.group is not None else dist.group.WORLD)
+            self._pad.zero_()
+            self._pad_ptrs = [int(a) for a in hdl.buffer_ptrs]
+            self._pad_handle = hdl
+            hdl.barrier(channel=0, timeout_ms=self.barrier_timeout_ms)     # every pad is zero before anyone signals
+        self._epoch += 1
+        return self._pad_ptrs, self.rank, self._epoch
 
     def probe(self) -> None:
         """Collective: allocate and rendezvous a tiny symmetric buffer, so that a box without NVLink

@@ -409,6 +409,183 @@ __global__ void __launch_bounds__(kLossThreads, (NV >= 16 ? 1 : 2)) loss_rows_in
 }
 
 // ---------------------------------------------------------------------------------------
+// Lean staged kernel (round 2): same tile pipeline as the STAGED variant above, with the per-sweep
+// overhead that made narrow rows issue-bound taken out (ncu r1: 8.07 M warp instructions for 79 MB at
+// 65536x100, 52 % issue-active at 23 % occupancy):
+//   * the label column is handled THROUGH the shared-memory tile: every lane of a row group reads the two
+//     label logits with one broadcast LDS each, lane 0 of the group then overwrites them with the mask
+//     value (DKD), and only then do the lanes pull their vectors -- no per-vector compare/select chains;
+//   * the label's gradient is one scalar store by lane 0 of the group after the row's vector stores
+//     (__syncwarp orders the two stores to that address), instead of a predicated add in every vector;
+//   * CFIX: the class count as a compile-time constant for the two standard datasets (100, 1000), so the
+//     tail guards, the row offsets inside the tile and the vector count fold away;
+//   * MINB: resident blocks per SM asked of the register allocator.
+// Arithmetic and summation order are those of loss_rows_in_registers; only the label column's gradient is
+// formed from scalars (same formula).
+// ---------------------------------------------------------------------------------------
+template <int LPR, int NV, int CFIX, bool DKD, int CE, bool SPLIT, int MINB>
+__global__ void __launch_bounds__(kLossThreads, MINB) loss_rows_lean(const LossArgs A) {
+    constexpr int GPW = 32 / LPR;  // rows per warp
+    const int C = CFIX ? CFIX : (int)A.classes;
+    const int nvec = C >> 2;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sub = lane % LPR, grp = lane / LPR;
+    const long long sweep = (long long)gridDim.x * kLossWarps * GPW;
+    double acc_kd = 0.0, acc_ce = 0.0;
+
+    extern __shared__ __align__(128) unsigned char staged_smem[];
+    const unsigned region = (unsigned)((2u * GPW * C * sizeof(float) + 127u) & ~127u);
+    unsigned long long *bar = reinterpret_cast<unsigned long long *>(staged_smem) + warp;
+    float *tile_s = reinterpret_cast<float *>(staged_smem + 128 + (size_t)warp * region);
+    float *tile_t = tile_s + GPW * C;
+    unsigned parity = 0;
+    const long long first = ((long long)blockIdx.x * kLossWarps + warp) * GPW;
+    auto issue_tile = [&](long long b) {
+        const long long left = A.rows - b;
+        const unsigned bytes = (unsigned)((left < GPW ? left : GPW) * C * sizeof(float));
+        mbar_expect_tx(bar, 2u * bytes);
+        bulk_g2s(tile_s, A.zs + b * C, bytes, bar);
+        bulk_g2s(tile_t, A.zt + b * C, bytes, bar);
+    };
+    if (threadIdx.x == 0) {
+        for (int w = 0; w < kLossWarps; ++w) mbar_init(reinterpret_cast<unsigned long long *>(staged_smem) + w, 1);
+        mbar_init_fence();
+    }
+    __syncthreads();
+    long long g_next = -1;
+    if (first < A.rows) {
+        if (lane == 0) issue_tile(first);
+        if (DKD || CE != 0) g_next = A.target[first + grp < A.rows ? first + grp : A.rows - 1];
+    }
+
+    const float4 *ps = reinterpret_cast<const float4 *>(tile_s + grp * C) + sub;
+    const float4 *pt = reinterpret_cast<const float4 *>(tile_t + grp * C) + sub;
+    constexpr float kLog2e = 1.4426950408889634f;
+
+    for (long long base = first; base < A.rows; base += sweep) {
+        const long long row = base + grp;
+        const bool live = row < A.rows;
+        const long long r = live ? row : A.rows - 1;
+        const long long g = g_next;
+        const bool has_label = (DKD || CE != 0) && g >= 0 && g < C;
+
+        mbar_wait(bar, parity);
+        parity ^= 1u;
+        float zsg = kNegBig, ztg = kNegBig;
+        if (DKD || CE != 0) {
+            if (has_label) {               // same address for the LPR lanes of a group: one broadcast read each
+                zsg = tile_s[grp * C + (int)g];
+                ztg = tile_t[grp * C + (int)g];
+            }
+            if (DKD) {
+                __syncwarp();              // every lane holds the label logits: now take them out of the row
+                if (has_label && sub == 0) tile_s[grp * C + (int)g] = tile_t[grp * C + (int)g] = kNegBig;
+                __syncwarp();
+            }
+        }
+        float4 s[NV], t[NV];
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            if (i * LPR + (LPR - 1) < (CFIX ? CFIX / 4 : 0) || sub + i * LPR < nvec) {
+                s[i] = ps[i * LPR];
+                t[i] = pt[i * LPR];
+            } else {
+                s[i] = t[i] = make_float4(kNegBig, kNegBig, kNegBig, kNegBig);
+            }
+        }
+        __syncwarp();                      // every lane has its copy: the tile may be overwritten
+        const long long nb = base + sweep;
+        if (nb < A.rows) {
+            if (lane == 0) {
+                fence_proxy_async_smem();
+                issue_tile(nb);
+            }
+            if (DKD || CE != 0) g_next = A.target[nb + grp < A.rows ? nb + grp : A.rows - 1];
+        }
+
+        // pass 1: maxima of the kept classes
+        float ms = kNegBig, mt = kNegBig;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            ms = fmaxf(ms, fmaxf(fmaxf(s[i].x, s[i].y), fmaxf(s[i].z, s[i].w)));
+            mt = fmaxf(mt, fmaxf(fmaxf(t[i].x, t[i].y), fmaxf(t[i].z, t[i].w)));
+        }
+        ms = group_max<LPR>(ms);
+        mt = group_max<LPR>(mt);
+        const float m1 = fmaxf(ms, zsg);
+
+        // pass 2: exponentials replace the logits in place; sums and the cross term
+        float Es = 0.f, Et = 0.f, W = 0.f, Z1 = 0.f;
+        float4 c1[CE == 2 ? NV : 1];
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            float4 e1 = make_float4(0.f, 0.f, 0.f, 0.f);
+#define MDB200_P2(c)                                                   \
+    {                                                                  \
+        const float ds = s[i].c - ms, dt = t[i].c - mt;                \
+        if (CE == 2) { e1.c = ex2_approx((s[i].c - m1) * kLog2e); Z1 += e1.c; } \
+        const float es = ex2_approx(ds * A.k2), et = ex2_approx(dt * A.k2);     \
+        Es += es; Et += et;                                            \
+        W = fmaf(et, dt - ds, W);                                      \
+        s[i].c = es; t[i].c = et;                                      \
+    }
+            MDB200_P2(x) MDB200_P2(y) MDB200_P2(z) MDB200_P2(w)
+#undef MDB200_P2
+            if (CE == 2) c1[i] = e1;
+        }
+        Es = group_sum<LPR>(Es);
+        Et = group_sum<LPR>(Et);
+        W = group_sum<LPR>(W);
+        if (CE == 2) Z1 = group_sum<LPR>(Z1);
+
+        const RowCoef k = row_coefficients<DKD, CE>(A, ms, mt, Es, Et, W, zsg, ztg, m1, Z1);
+        if (live && sub == 0) {
+            acc_kd += (double)k.loss_kd;
+            if (CE != 0) acc_ce += (double)k.loss_ce;
+        }
+
+        // pass 3: gradient rows (the label column is patched afterwards)
+        float4 *pg = reinterpret_cast<float4 *>(A.gkd + r * A.ld_g) + sub;
+        float4 *pc = SPLIT ? reinterpret_cast<float4 *>(A.gce + r * A.ld_g) + sub : nullptr;
+        const float nct = -k.ct;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            float4 gk, gc4;
+#define MDB200_P3(c)                                                   \
+    {                                                                  \
+        gk.c = fmaf(k.cs, s[i].c, nct * t[i].c);                       \
+        if (CE != 0) {                                                 \
+            const float ce = k.cce * (CE == 2 ? c1[CE == 2 ? i : 0].c : s[i].c); \
+            if (SPLIT) gc4.c = ce; else gk.c += ce;                    \
+        }                                                              \
+    }
+            MDB200_P3(x) MDB200_P3(y) MDB200_P3(z) MDB200_P3(w)
+#undef MDB200_P3
+            if (live && (i * LPR + (LPR - 1) < (CFIX ? CFIX / 4 : 0) || sub + i * LPR < nvec)) {
+                st_stream(pg + i * LPR, gk);
+                if (SPLIT) st_stream(pc + i * LPR, gc4);
+            }
+        }
+        if (DKD || CE != 0) {
+            __syncwarp();                  // the row's vector stores come first: the patch below must land last
+            if (live && has_label && sub == 0) {
+                // the label column from scalars; for DKD its exponentials were masked to exactly 0
+                const float esg = DKD ? 0.f : ex2_approx((zsg - ms) * A.k2);
+                const float etg = DKD ? 0.f : ex2_approx((ztg - mt) * A.k2);
+                float vk = fmaf(k.cs, esg, nct * etg) + k.gt_kd;
+                if (CE != 0) {
+                    const float e_ce = DKD ? 0.f : (CE == 2 ? ex2_approx((zsg - m1) * kLog2e) : esg);
+                    const float vc = k.cce * e_ce + k.gt_ce;
+                    if (SPLIT) A.gce[r * A.ld_g + g] = vc; else vk += vc;
+                }
+                A.gkd[r * A.ld_g + g] = vk;
+            }
+        }
+    }
+    cta_reduce_and_publish(A, acc_kd, acc_ce);
+}
+
+// ---------------------------------------------------------------------------------------
 // Generic kernel: any class count / alignment.  One CTA per row, three sweeps over the
 // row (the 2nd and 3rd hit L1/L2), scalar coalesced accesses.
 // ---------------------------------------------------------------------------------------
@@ -603,6 +780,31 @@ static cudaError_t launch_staged(const LossArgs &A, const LaunchCtx &ctx) {
     return cudaGetLastError();
 }
 
+template <int LPR, int NV, int CFIX, bool DKD, int CE, bool SPLIT, int MINB>
+static cudaError_t launch_lean(const LossArgs &A, const LaunchCtx &ctx) {
+    constexpr int GPW = 32 / LPR;
+    constexpr int rows_per_cta = kLossWarps * GPW;
+    auto kernel = loss_rows_lean<LPR, NV, CFIX, DKD, CE, SPLIT, MINB>;
+    const size_t region = (2 * (size_t)GPW * A.classes * sizeof(float) + 127) & ~(size_t)127;
+    const size_t smem = 128 + kLossWarps * region;
+    static PerDeviceInt configured, occ_cache, occ_smem;
+    if (cudaError_t e = ensure_dynamic_smem(kernel, ctx.dev, smem, configured)) return e;
+    const int occ = resident_ctas_per_sm(kernel, ctx.dev, smem, occ_cache, &occ_smem);
+    long long want = (A.rows + rows_per_cta - 1) / rows_per_cta;
+    const long long cap = (long long)ctx.sms * occ;
+    if (want > cap) want = cap;
+    if (want > kMaxCtas) want = kMaxCtas;
+    if (cudaError_t e = before_launch(A, ctx, want)) return e;
+    kernel<<<(unsigned)want, kLossThreads, smem, ctx.st>>>(A);
+    return cudaGetLastError();
+}
+
+// MDB200_LOSS_LEAN: 0 = round-1 staged kernels, 1 (default) = lean kernels (A/B timing knob)
+static int lean_variant() {
+    static const int v = getenv("MDB200_LOSS_LEAN") ? atoi(getenv("MDB200_LOSS_LEAN")) : 1;
+    return v;
+}
+
 template <bool DKD, int CE, bool SPLIT>
 static cudaError_t launch_shape(const LossArgs &A, bool vec_ok, const LaunchCtx &ctx) {
     const long long nvec = A.classes >> 2;
@@ -611,6 +813,15 @@ static cudaError_t launch_shape(const LossArgs &A, bool vec_ok, const LaunchCtx 
     // MDB200_LOSS_STAGED=0 switches them off for A/B timing.
     static const bool staged = !(getenv("MDB200_LOSS_STAGED") && atoi(getenv("MDB200_LOSS_STAGED")) == 0);
     if (staged && vec_ok && A.ld_s == A.classes && A.ld_t == A.classes) {
+        // lean kernels where they measured faster on B200 (profiles/r2_loss_ab.txt): -8 % at 65536x100 (DKD, KD), -3..-5 % on
+        // 1000-class rows up to 32 K rows; the general-T cross entropy next to DKD keeps a third register row and
+        // spills there, so that one combination stays on the round-1 kernel
+        const int lean = lean_variant();
+        const bool third_row = DKD && CE == 2;
+        if (lean >= 1 && A.classes == 100 && !third_row) return launch_lean<4, 7, 100, DKD, CE, SPLIT, 2>(A, ctx);
+        if (lean >= 1 && A.classes == 1000 && A.rows <= 32768 && CE != 2) return launch_lean<32, 8, 1000, DKD, CE, SPLIT, 2>(A, ctx);
+        if (lean >= 1 && nvec <= 28 && !third_row) return launch_lean<4, 7, 0, DKD, CE, SPLIT, 2>(A, ctx);
+        if (lean >= 1 && nvec <= 32 && !third_row) return launch_lean<8, 4, 0, DKD, CE, SPLIT, 2>(A, ctx);
         if (nvec <= 28) return launch_staged<4, 7, DKD, CE, SPLIT>(A, ctx);
         if (nvec <= 32) return launch_staged<8, 4, DKD, CE, SPLIT>(A, ctx);
         if (nvec > 128 && nvec <= 256 && A.rows <= 32768) return launch_staged<32, 8, DKD, CE, SPLIT>(A, ctx);

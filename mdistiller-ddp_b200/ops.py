@@ -251,11 +251,13 @@ def dot_step_fused(p_local: torch.Tensor, g_task_local: torch.Tensor, g_kd_local
                    v_task: Optional[torch.Tensor], v_kd: torch.Tensor, *, multicast=None, peers=None,
                    kd_is_reduced: bool, shard_lo: int, shard_len: int, world: int, lr: float, momentum: float,
                    momentum_kd: float, weight_decay: float = 0.0, dampening: float = 0.0, grad_scale: float = 1.0,
-                   first_task: bool = False, first_kd: bool = False) -> None:
+                   first_task: bool = False, first_kd: bool = False, sync=None) -> None:
     """Fused reduce + DOT update + broadcast for this rank's shard (see mdb200_dot_step_fused).
 
     ``multicast`` = (p_mc, g_task_mc, g_kd_mc) integer multicast addresses or None;
-    ``peers`` = (p_ptrs, g_task_ptrs, g_kd_ptrs), each a list of ``world`` integer base addresses.
+    ``peers`` = (p_ptrs, g_task_ptrs, g_kd_ptrs), each a list of ``world`` integer base addresses;
+    ``sync`` = (pad addresses of every rank, this rank, epoch) for the in-kernel handshake, or None when the
+    caller brackets the launch with barriers itself.
     """
     global launch_count
     import ctypes as C
@@ -277,6 +279,37 @@ def dot_step_fused(p_local: torch.Tensor, g_task_local: torch.Tensor, g_kd_local
         rc = lib.mdb200_dot_step_fused(
             ptrs[0], mc[0] or None, tabs[0], ptrs[1], mc[1] or None, tabs[1], ptrs[2], mc[2] or None, tabs[2],
             int(kd_is_reduced), ptrs[3], ptrs[4], shard_lo, shard_len, world, lr, momentum, momentum_kd,
-            weight_decay, dampening, grad_scale, int(first_task), int(first_kd), _stream_ptr(p_local.device))
+            weight_decay, dampening, grad_scale, int(first_task), int(first_kd),
+            table(sync[0]) if sync is not None else None, int(sync[1]) if sync is not None else 0,
+            int(sync[2]) if sync is not None else 0, _stream_ptr(p_local.device))
     _lib.check(rc, "mdb200_dot_step_fused")
+    launch_count += 1
+
+
+def sgd_step_fused(p_local: torch.Tensor, g_local: torch.Tensor, v: Optional[torch.Tensor], *, multicast=None, peers=None,
+                   shard_lo: int, shard_len: int, world: int, lr: float, momentum: float, weight_decay: float = 0.0,
+                   dampening: float = 0.0, grad_scale: float = 1.0, first_step: bool = False, sync=None) -> None:
+    """Fused reduce + momentum SGD + broadcast for this rank's shard (see mdb200_sgd_step_fused).
+    ``multicast`` = (p_mc, g_mc) or None; ``peers`` = (p_ptrs, g_ptrs); ``sync`` as in dot_step_fused."""
+    global launch_count
+    import ctypes as C
+    lib = _lib.load()
+    n = p_local.numel()
+    ptrs = (_flat_ptr(p_local, "p_local", n), _flat_ptr(g_local, "g_local", n), _flat_ptr(v, "v", shard_len))
+    mc = multicast if multicast is not None else (None, None)
+
+    def table(addrs):
+        if addrs is None:
+            return None
+        return (C.c_void_p * world)(*[int(a) for a in addrs])
+
+    pt = peers if peers is not None else (None, None)
+    tabs = [table(t) for t in pt]
+    with torch.cuda.device(p_local.device):
+        rc = lib.mdb200_sgd_step_fused(
+            ptrs[0], mc[0] or None, tabs[0], ptrs[1], mc[1] or None, tabs[1], ptrs[2], shard_lo, shard_len, world,
+            lr, momentum, weight_decay, dampening, grad_scale, int(first_step),
+            table(sync[0]) if sync is not None else None, int(sync[1]) if sync is not None else 0,
+            int(sync[2]) if sync is not None else 0, _stream_ptr(p_local.device))
+    _lib.check(rc, "mdb200_sgd_step_fused")
     launch_count += 1

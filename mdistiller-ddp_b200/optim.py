@@ -370,15 +370,18 @@ class DistillationOrientedTrainer(_FlatOptimizer):
         p, gt, gk = sp.flat, self._buckets["task"], self._buckets["kd"]
         (p_mc, p_peers), (gt_mc, gt_peers), (gk_mc, gk_peers) = (comm.addresses(t) for t in (p, gt, gk))
         use_mc = bool(p_mc and gt_mc and gk_mc)
-        self.last_fused = {"multicast": use_mc, "kd_in_kernel": not self._kd_prereduced}
-        comm.barrier(p, channel=0)          # every rank's second backward (and KD reduce-scatter) has landed
+        sync = comm.next_sync()
+        self.last_fused = {"multicast": use_mc, "kd_in_kernel": not self._kd_prereduced, "in_kernel_sync": sync is not None}
+        if sync is None:
+            comm.barrier(p, channel=0)      # every rank's second backward (and KD reduce-scatter) has landed
         self._k.dot_step_fused(
             p, gt, gk, self._v_task if hp["momentum"] != 0 else None, self._v_kd,
             multicast=(p_mc, gt_mc, gk_mc) if use_mc else None,
             peers=None if use_mc else (p_peers, gt_peers, gk_peers),
             kd_is_reduced=self._kd_prereduced, shard_lo=sp.shard_lo, shard_len=sp.shard_len,
-            world=comm.world_size, first_task=first_t, first_kd=first_k, **hp)
-        comm.barrier(p, channel=1)          # nobody reads P before every shard owner has written it
+            world=comm.world_size, first_task=first_t, first_kd=first_k, sync=sync, **hp)
+        if sync is None:
+            comm.barrier(p, channel=1)      # nobody reads P before every shard owner has written it
 
     # -- reference checkpoint layout: state[p]['momentum_buffer'|'momentum_kd_buffer'] -----
     def _state_pairs(self):
@@ -425,6 +428,7 @@ class FlatSGD(_FlatOptimizer):
         self._v = self._space.new_shard_buffer()
         self._has_v = [False] * len(self._space.params)
         self.max_grad_norm = 0.0      # SOLVER.GRAD_CLIP; > 0 clips the global gradient norm inside step()
+        self.last_fused = None        # set by every fused step, like the DOT optimizer's
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -434,21 +438,43 @@ class FlatSGD(_FlatOptimizer):
                 loss = closure()
         group = self.param_groups[0]
         members = self._collect("grad")
-        work = self._comm.reduce_scatter_sum(self._buckets["grad"], async_op=True)
-        if work is not None:
-            work.wait()
-        clip = self._clip_coefficient(self._buckets["grad"], self.max_grad_norm)
         momentum = group["momentum"]
         modes = [((_TASK if t else _NONE), t and not self._has_v[i], False) for i, t in enumerate(members)]
         sp = self._space
-        for lo, hi, (_, first, _) in self._runs(modes):
-            a, b = lo - sp.shard_lo, hi - sp.shard_lo
-            self._k.sgd_step(sp.flat[lo:hi], self._buckets["grad"][lo:hi],
-                             self._v[a:b] if momentum != 0 else None,
-                             lr=group["lr"], momentum=momentum, weight_decay=group["weight_decay"],
-                             dampening=group["dampening"], grad_scale=1.0 / self._comm.world_size,
-                             first_step=first, grad_scale_dev=clip)
-        self._comm.all_gather(sp.flat)
+        comm = self._comm
+        # one fused kernel over NVLink (gradient sum over ranks -> SGD on the shard -> parameters to every rank)
+        # when every parameter has a gradient with the same first-step flag -- a GLOBAL property, so all ranks
+        # agree -- and no clipping norm has to be formed from the reduced gradient first
+        fused = (getattr(comm, "fused", False) and comm.world_size > 1 and not (self.max_grad_norm and self.max_grad_norm > 0)
+                 and modes[0][0] == _TASK and all(m == modes[0] for m in modes))
+        if fused:
+            p, g = sp.flat, self._buckets["grad"]
+            (p_mc, p_peers), (g_mc, g_peers) = comm.addresses(p), comm.addresses(g)
+            use_mc = bool(p_mc and g_mc)
+            sync = comm.next_sync()
+            self.last_fused = {"multicast": use_mc, "kd_in_kernel": False, "in_kernel_sync": sync is not None}
+            if sync is None:
+                comm.barrier(p, channel=0)
+            self._k.sgd_step_fused(p, g, self._v if momentum != 0 else None,
+                                   multicast=(p_mc, g_mc) if use_mc else None, peers=None if use_mc else (p_peers, g_peers),
+                                   shard_lo=sp.shard_lo, shard_len=sp.shard_len, world=comm.world_size, lr=group["lr"],
+                                   momentum=momentum, weight_decay=group["weight_decay"], dampening=group["dampening"],
+                                   grad_scale=1.0 / comm.world_size, first_step=modes[0][1], sync=sync)
+            if sync is None:
+                comm.barrier(p, channel=1)
+        else:
+            work = comm.reduce_scatter_sum(self._buckets["grad"], async_op=True)
+            if work is not None:
+                work.wait()
+            clip = self._clip_coefficient(self._buckets["grad"], self.max_grad_norm)
+            for lo, hi, (_, first, _) in self._runs(modes):
+                a, b = lo - sp.shard_lo, hi - sp.shard_lo
+                self._k.sgd_step(sp.flat[lo:hi], self._buckets["grad"][lo:hi],
+                                 self._v[a:b] if momentum != 0 else None,
+                                 lr=group["lr"], momentum=momentum, weight_decay=group["weight_decay"],
+                                 dampening=group["dampening"], grad_scale=1.0 / comm.world_size,
+                                 first_step=first, grad_scale_dev=clip)
+            comm.all_gather(sp.flat)
         if momentum != 0:
             for i, t in enumerate(members):
                 if t:

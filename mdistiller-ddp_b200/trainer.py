@@ -73,9 +73,11 @@ class TailStepMixin:
             return None
         world = dist.get_world_size()
         mode = resolve_comm_mode(self.comm_mode, world)
-        if mode != "nccl" and world > 1 and self.trainer_kind == "dot":
+        fusable = self.trainer_kind == "dot" or self.__dict__.get("_base_solver", "SGD") == "SGD"
+        if mode != "nccl" and world > 1 and fusable:
             try:
-                comm = SymmetricShardComm(fuse_kd=mode.startswith("fused_kd"), use_multicast=not mode.endswith("p2p"))
+                comm = SymmetricShardComm(fuse_kd=mode.startswith("fused_kd"), use_multicast=not mode.endswith("p2p"),
+                                          in_kernel_sync=os.environ.get("MDB200_FUSED_SYNC", "pad") != "barrier")
                 comm.probe()                    # allocation + rendezvous work on this box?
                 self.comm_mode_used = mode
                 return comm
@@ -89,6 +91,7 @@ class TailStepMixin:
     def init_optimizer(self, cfg):
         core = _unwrap(self.distiller)
         silence_ddp_reducer(self.distiller)
+        self._base_solver = cfg.SOLVER.TYPE          # the fused NVLink step exists for DOT and for momentum SGD
         comm = self._make_comm()
         params = core.get_learnable_parameters()
         if self.trainer_kind == "dot":

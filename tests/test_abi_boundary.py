@@ -30,7 +30,7 @@ def lib():
 def test_header_declares_the_expected_surface():
     assert set(_declared()) >= {"mdb200_abi_version", "mdb200_error_string", "mdb200_loss_workspace_bytes",
                                 "mdb200_distill_loss", "mdb200_scale_by_device_scalar", "mdb200_dot_step",
-                                "mdb200_sgd_step", "mdb200_dot_step_fused", "mdb200_distill_loss_static_scratch",
+                                "mdb200_sgd_step", "mdb200_dot_step_fused", "mdb200_sgd_step_fused", "mdb200_distill_loss_static_scratch",
                                 "mdb200_adam_step", "mdb200_sum_squares", "mdb200_clip_coefficient", "mdb200_gather_flat", "mdb200_metrics_record"}
 
 
@@ -42,7 +42,7 @@ def test_every_declared_symbol_is_exported_and_bound(lib):
 
 
 def test_version_and_error_strings(lib):
-    assert lib.mdb200_abi_version() == 2
+    assert lib.mdb200_abi_version() == 3
     assert lib.mdb200_error_string(0) == b"ok"
     assert b"workspace" in lib.mdb200_error_string(-3)
     assert lib.mdb200_loss_workspace_bytes() >= 64 + 2 * 8 * 1184
@@ -67,11 +67,21 @@ def test_argument_errors_are_reported_before_any_cuda_work(lib):
     assert lib.mdb200_sgd_step(p, p, None, 16, .1, .9, 0., 0., 1., None, 0, None) == -1            # momentum needs v
     fused = lambda **kw: lib.mdb200_dot_step_fused(  # noqa: E731
         kw.get("p", p), None, None, p, None, None, p, None, None, 1, p, p, kw.get("lo", 0), kw.get("n", 16),
-        kw.get("world", 2), .1, .9, .9, 0., 0., .5, 0, 0, None)
+        kw.get("world", 2), .1, .9, .9, 0., 0., .5, 0, 0, kw.get("pads"), kw.get("rank", 0), 1, None)
     assert fused() == -1                       # neither multicast addresses nor peer tables
     assert fused(world=17) == -1               # more peers than the kernel addresses
     assert fused(lo=2) == -4                   # shard must start on a 16-byte slot
     assert fused(p=None) == -1
+    sgd_fused = lambda **kw: lib.mdb200_sgd_step_fused(  # noqa: E731
+        kw.get("p", p), kw.get("mc"), kw.get("peers"), p, kw.get("mc"), kw.get("peers"), kw.get("v", p), kw.get("lo", 0), 16,
+        kw.get("world", 2), .1, kw.get("m", .9), 0., 0., .5, 0, kw.get("pads"), kw.get("rank", 0), 1, None)
+    assert sgd_fused() == -1                   # neither multicast addresses nor peer tables
+    assert sgd_fused(world=0) == -1 and sgd_fused(lo=6) == -4 and sgd_fused(p=None) == -1
+    assert sgd_fused(v=None, mc=p) == -1       # momentum needs its buffer
+    two = (ctypes.c_void_p * 2)(p, None)
+    assert sgd_fused(peers=two) == -1          # a peer's base address is missing
+    two = (ctypes.c_void_p * 2)(p, p)
+    assert sgd_fused(peers=two, pads=two, rank=2) == -1      # rank outside the world
     assert lib.mdb200_adam_step(p, p, p, p, 16, 1e-3, .9, .999, 1e-8, 0., 0, 0, 1., None, None) == -1   # step is 1-based
     assert lib.mdb200_sum_squares(p, 16, 1., p, p, 16, None) == -3
     assert lib.mdb200_clip_coefficient(p, 0., p, None) == -1

@@ -25,8 +25,9 @@ def _make_comm(mode):
     from mdistiller_ddp_b200.comm import ShardComm, SymmetricShardComm
     if mode == "nccl":
         return ShardComm()
-    return SymmetricShardComm(fuse_kd=(mode in ("fused_kd", "fused_kd_p2p")),
-                              use_multicast=not mode.endswith("p2p"), barrier_timeout_ms=15000)
+    mode, _, sync = mode.partition("+")        # "+barrier": bracket the kernel with barrier launches instead of the sync pad
+    return SymmetricShardComm(fuse_kd=(mode in ("fused_kd", "fused_kd_p2p")), use_multicast=not mode.endswith("p2p"),
+                              barrier_timeout_ms=15000, in_kernel_sync=(sync != "barrier"))
 
 
 def _opt_worker(rank, world, port, case_idx, out, mode="nccl"):
@@ -74,8 +75,9 @@ def _opt_worker(rank, world, port, case_idx, out, mode="nccl"):
     (2, 0, "nccl"), (2, 2, "nccl"), (4, 6, "nccl"), (8, 6, "nccl"),
     # one fused kernel over NVLink symmetric memory: NVLS multicast, both buckets in-switch, plain peer access
     (2, 0, "fused"), (2, 6, "fused_kd"), (2, 6, "fused_p2p"), (2, 2, "fused"),
+    (2, 6, "fused_p2p+barrier"), (2, 6, "fused_kd+barrier"),
     (4, 6, "fused_kd"), (4, 0, "fused_p2p"),
-    (8, 6, "fused"), (8, 6, "fused_kd"), (8, 6, "fused_kd_p2p"),
+    (8, 6, "fused"), (8, 6, "fused_kd"), (8, 6, "fused_kd_p2p"), (8, 6, "fused_kd+barrier"),
 ])
 def test_sharded_dot_step_matches_oracle_on_rank_averaged_gradients(world, case_idx, mode, tmp_path):
     _need_gpus(world)
@@ -101,6 +103,69 @@ def test_sharded_dot_step_matches_oracle_on_rank_averaged_gradients(world, case_
             assert oracle.max_rel_err(got["state"][i]["momentum_kd_buffer"], ref.buf_kd[i]) <= 1e-5
         if ref.buf_task[i] is not None:
             assert oracle.max_rel_err(got["state"][i]["momentum_buffer"], ref.buf_task[i]) <= 1e-5
+
+
+def _sgd_worker(rank, world, port, case_idx, out, mode):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        import mdistiller_ddp_b200 as b200
+        case = _cases.DOT_CASES[case_idx]
+        params = [torch.nn.Parameter((p.clone() + (0.5 if rank else 0.0)).cuda()) for p in _cases.make_params(case)]
+        opt = b200.FlatSGD(params, lr=case.lr, momentum=case.momentum, weight_decay=case.wd, comm=_make_comm(mode))
+        shapes = [p.shape for p in params]
+        f = 1.0 - 0.5 * (rank - (world - 1) / 2)          # per-rank gradient factor, mean 1 over ranks
+        fused_steps = 0
+        for step in range(12):
+            if step == 6:
+                opt.param_groups[0]["lr"] = case.lr * 0.1
+            _, task = _cases.make_grads(case, step, shapes)
+            opt.zero_grad()
+            for p, g in zip(params, task):
+                p.grad = (g * f).cuda()
+            opt.last_fused = None
+            opt.step()
+            fused_steps += opt.last_fused is not None
+        assert fused_steps == (0 if mode == "nccl" else 12), "the fused kernel must have served every step"
+        flat = opt.flat_params.clone()
+        gathered = [torch.empty_like(flat) for _ in range(world)]
+        dist.all_gather(gathered, flat)
+        assert all(torch.equal(g, flat) for g in gathered), "ranks diverged"
+        opt.sync_checkpoint_state()
+        if rank == 0:
+            sd = opt.state_dict()
+            torch.save({"p": [p.detach().cpu() for p in params],
+                        "v": [sd["state"][i]["momentum_buffer"].cpu() for i in range(len(params))]}, out)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,mode", [(2, "nccl"), (2, "fused_p2p"), (2, "fused"), (2, "fused_p2p+barrier"),
+                                        (4, "fused_p2p"), (8, "fused"), (8, "fused_p2p")])
+def test_sharded_sgd_step_matches_torch_sgd_on_rank_averaged_gradients(world, mode, tmp_path):
+    """Base trainer's data-parallel step (BaseTrainer + DDP all-reduce + optim.SGD, trainer.py:86-91,303-321): NCCL
+    launches and the fused NVLink kernel against torch.optim.SGD fed the rank-averaged gradient."""
+    _need_gpus(world)
+    case_idx = 6
+    out = str(tmp_path / "r0.pt")
+    port = 29100 + (os.getpid() % 300) + world * 7 + len(mode)
+    mp.spawn(_sgd_worker, args=(world, port, case_idx, out, mode), nprocs=world, join=True)
+    got = torch.load(out, weights_only=False)
+    case = _cases.DOT_CASES[case_idx]
+    params = [torch.nn.Parameter(p.clone()) for p in _cases.make_params(case)]
+    ref = torch.optim.SGD(params, lr=case.lr, momentum=case.momentum, weight_decay=case.wd)
+    shapes = [p.shape for p in params]
+    for step in range(12):
+        if step == 6:
+            ref.param_groups[0]["lr"] = case.lr * 0.1
+        _, task = _cases.make_grads(case, step, shapes)
+        for p, g in zip(params, task):
+            p.grad = g.clone()
+        ref.step()
+    for p, q, v in zip(got["p"], params, got["v"]):
+        assert oracle.max_rel_err(p, q.detach()) <= 1e-5
+        assert oracle.max_rel_err(v, ref.state[q]["momentum_buffer"]) <= 1e-5
 
 
 def _trainer_worker(rank, world, port):

@@ -8,9 +8,15 @@ DDP reducer) and once after ``mdistiller_ddp_b200.install()`` -- same yaml, same
 the reference's own ResNet32x4 -> ResNet8x4 backbones, its epoch loop, validation, logging and checkpointing.
 What the two runs leave in ``student_latest`` / ``latest`` must agree.
 
-Tolerance: rel 1e-4 (max|a-b| / max|b| per tensor) on the student weights and the optimizer momenta after the
-epoch -- looser than the kernels' own 1e-5 because between the two runs everything upstream of the logits is
-cuDNN fp32 (TF32 off) whose algorithm choice (`cudnn.benchmark = True`, tools/train.py:9) may differ run to run.
+Tolerance.  Two runs of the REFERENCE ITSELF do not agree bit for bit on a GPU: cuDNN's backward kernels sum in
+a run-dependent order, and a few tensors amplify that (BatchNorm biases start at zero and their gradients are
+small differences of large sums: measured on B200 after 5 iterations, reference vs reference differs by up to
+4e-2 there, 2e-3 on the stem convolution, 3e-4 on the median weight tensor; profiles/r2_dropin_noise.txt).  So
+every variant is run TWICE and each tensor is held to
+    |ours - ref| <= max(1e-4, 8 x the larger of the two run-to-run distances of that tensor)       (rel = / max|ref|)
+i.e. the patched run must be indistinguishable from the reference's own repeatability, tensor by tensor; with one
+iteration, where that noise is ~1e-6, this is a tight comparison, with five it follows the drift.  The file sorts
+near the end of the GPU tests so that a `-x` run has been through the kernel parity tests first.
 """
 
 import os
@@ -24,6 +30,7 @@ import oracle
 pytestmark = pytest.mark.gpu
 
 TOL = 1e-4
+NOISE_FACTOR = 8.0
 DOT_YAML = "configs/cifar100/dot/res32x4_res8x4.yaml"      # KD + DOT trainer   (BASELINE.json configs[1])
 DKD_YAML = "configs/cifar100/dkd/res32x4_res8x4.yaml"      # DKD + base trainer (BASELINE.json configs[0])
 
@@ -34,23 +41,33 @@ def _staged():
         pytest.skip("no reference tree staged (run oracle/make_ref.sh in the build container)")
 
 
-def _compare(ours, ref, momenta):
-    assert set(ours["student"]) == set(ref["student"])
-    worst = 0.0
-    for k, v in ref["student"].items():
-        if v.dtype.is_floating_point:
-            worst = max(worst, oracle.max_rel_err(ours["student"][k], v))
-        else:
-            assert torch.equal(ours["student"][k], v), k            # num_batches_tracked
-    assert worst <= TOL, worst
-    so, sr = ours["latest"]["optimizer"], ref["latest"]["optimizer"]
-    assert so["param_groups"][0]["lr"] == sr["param_groups"][0]["lr"]
-    assert set(so["state"]) == set(sr["state"])
-    for i, st in sr["state"].items():
-        assert set(so["state"][i]) >= set(momenta) and set(st) >= set(momenta)
+def _tensors(run, momenta):
+    """Everything the run left behind as {name: tensor}: student weights + BatchNorm statistics + optimizer momenta."""
+    out = dict(run["student"])
+    for i, st in run["latest"]["optimizer"]["state"].items():
+        assert set(st) >= set(momenta), (i, set(st))
         for key in momenta:
-            assert oracle.max_rel_err(so["state"][i][key], st[key]) <= TOL, (i, key)
-    return worst
+            out[f"optimizer.state[{i}].{key}"] = st[key]
+    return out
+
+
+def _compare(ours_pair, ref_pair, momenta):
+    """ours vs reference, tensor by tensor, against the run-to-run repeatability of both (see the module docstring)."""
+    o1, o2, r1, r2 = (_tensors(x, momenta) for x in (*ours_pair, *ref_pair))
+    assert set(o1) == set(r1)
+    assert ours_pair[0]["latest"]["optimizer"]["param_groups"][0]["lr"] == ref_pair[0]["latest"]["optimizer"]["param_groups"][0]["lr"]
+    report = []
+    for k, v in r1.items():
+        if not v.dtype.is_floating_point:
+            assert torch.equal(o1[k], v), k                        # num_batches_tracked
+            continue
+        noise = max(oracle.max_rel_err(r2[k], v), oracle.max_rel_err(o2[k], o1[k]))
+        err = oracle.max_rel_err(o1[k], v)
+        report.append((err / max(TOL, NOISE_FACTOR * noise), err, noise, k))
+    report.sort(reverse=True)
+    assert report[0][0] <= 1.0, "ours vs reference beyond the reference's own repeatability: " + "; ".join(
+        f"{k}: err {e:.2e}, run-to-run {n:.2e}" for _, e, n, k in report[:4])
+    return report
 
 
 @pytest.mark.parametrize("yaml_path,momenta", [(DOT_YAML, ("momentum_buffer", "momentum_kd_buffer")),
@@ -58,10 +75,16 @@ def _compare(ours, ref, momenta):
 def test_unchanged_train_py_with_install_matches_the_reference_run(yaml_path, momenta, tmp_path):
     _staged()
     from oracle import ref_harness
-    ref = ref_harness.run_train(yaml_path, patched=False, out_dir=str(tmp_path / "ref"), iters=5, batch=64)
-    ours = ref_harness.run_train(yaml_path, patched=True, out_dir=str(tmp_path / "ours"), iters=5, batch=64)
-    assert ref["launches"] == 0 and ours["launches"] >= 5 * 3, "the patched run must go through the sm_100a kernels"
-    _compare(ours, ref, momenta)
+    for iters in (1, 5):
+        run = lambda tag, patched: ref_harness.run_train(yaml_path, patched=patched, out_dir=str(tmp_path / f"{tag}_{iters}"),
+                                                         iters=iters, batch=64)
+        ref, ref_again = run("ref_a", False), run("ref_b", False)
+        ours, ours_again = run("ours_a", True), run("ours_b", True)
+        assert ref["launches"] == 0 and ours["launches"] >= iters * 3, "the patched run must go through the sm_100a kernels"
+        report = _compare((ours, ours_again), (ref, ref_again), momenta)
+        if iters == 1:      # one step in: tensors whose repeatability is tight are matched tightly
+            tight = [e for _, e, n, _ in report if n <= 1e-6]
+            assert tight and max(tight) <= TOL
     # the progress of both runs is the same story: same losses in the epoch log (worklog.txt, 4 decimals)
     pick = lambda w: [l.strip() for l in w.splitlines() if l.strip().startswith(("ce:", "kd:", "train_acc"))]
     for a, b in zip(pick(ours["worklog"]), pick(ref["worklog"])):
@@ -75,13 +98,12 @@ def _two_gpu_worker(rank, port, out):
     torch.cuda.set_device(rank)
     from oracle import ref_harness
     res = {}
-    next_port = iter(range(port, port + 3))
+    next_port = iter(range(port, port + 5))
     use_port = lambda: os.environ.update(MASTER_PORT=str(next(next_port)))     # a fresh rendezvous per run
     # base trainer: the reference's DDP averages the one gradient set correctly, so its 2-GPU run IS the oracle
-    use_port()
-    res["ref"] = ref_harness.run_train(DKD_YAML, patched=False, out_dir=os.path.join(out, f"ref{rank}"), iters=4, batch=32)
-    use_port()
-    res["ours"] = ref_harness.run_train(DKD_YAML, patched=True, out_dir=os.path.join(out, f"ours{rank}"), iters=4, batch=32)
+    for tag, patched in (("ref", False), ("ref_again", False), ("ours", True), ("ours_again", True)):
+        use_port()
+        res[tag] = ref_harness.run_train(DKD_YAML, patched=patched, out_dir=os.path.join(out, f"{tag}{rank}"), iters=4, batch=32)
     # DOT trainer: the reference's own 2-GPU run leaves the task gradient rank-local, so only ours
     # runs -- through the epoch end, where the reference's loop asks rank 0 ALONE for optimizer.state_dict()
     use_port()
@@ -95,9 +117,9 @@ def test_unchanged_train_py_on_two_gpus_matches_the_reference_ddp_run(tmp_path):
     _staged()
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    mp.spawn(_two_gpu_worker, args=(29750 + 3 * (os.getpid() % 60), str(tmp_path)), nprocs=2, join=True)
+    mp.spawn(_two_gpu_worker, args=(29750 + 5 * (os.getpid() % 40), str(tmp_path)), nprocs=2, join=True)
     res = torch.load(str(tmp_path / "rank0.pt"), weights_only=False)
-    _compare(res["ours"], res["ref"], ("momentum_buffer",))
+    _compare((res["ours"], res["ours_again"]), (res["ref"], res["ref_again"]), ("momentum_buffer",))
     dot = res["dot"]
     assert dot["latest"]["epoch"] == 2 and dot["launches"] > 0
     st = dot["latest"]["optimizer"]["state"]
