@@ -625,6 +625,7 @@ def run_b200_arm(args):
     ops.dot_step = wrap("dot", orig_dot)
     ops.sgd_step = wrap("dot", ops.sgd_step)
     ops.dot_step_fused = wrap("dot", orig_fused)
+    ops.sgd_step_fused = wrap("dot", ops.sgd_step_fused)
     ops.distill_loss = wrap("loss", orig_loss)
     # losses.py / optim.py call through the `ops` module attribute, so the wrappers are seen
 
@@ -710,14 +711,17 @@ def run_b200_arm(args):
                     "note": "timed in-step right after backward: part of the 234 MB working set is L2-resident"}
     else:
         # fused reduce + update + broadcast kernel: the bytes that must cross NVLink bound it, not HBM
-        S, W = 4 * shard_elems, world
+        S, Wn = 4 * shard_elems, world
         nb = 2 if fused_info["kd_in_kernel"] else 1
+        if fused_info.get("in_kernel_sync"):
+            fused_info = dict(fused_info, note="us_per_launch includes the in-kernel wait for the slowest rank")
         if fused_info["multicast"]:     # every replica of a bucket shard travels to the switch once; P comes back W times
-            out_b, in_b = nb * W * S + S, nb * S + W * S
+            out_b, in_b = nb * Wn * S + S, nb * S + Wn * S
         else:
-            out_b, in_b = nb * (W - 1) * S + (W - 1) * S, nb * (W - 1) * S + (W - 1) * S
+            out_b, in_b = nb * (Wn - 1) * S + (Wn - 1) * S, nb * (Wn - 1) * S + (Wn - 1) * S
         link = max(out_b, in_b)
-        roofline = {"kernel": "dot_fused_shard (mdb200_dot_step_fused)", "bound": "nvlink",
+        roofline = {"kernel": "dot_fused_shard (mdb200_dot_step_fused)" if is_dot else "dot_fused_shard<HAS_KD=false> (mdb200_sgd_step_fused)",
+                    "bound": "nvlink",
                     "achieved": link / dot_avg / 1e9, "peak": 770.0, "unit": "GB/s", "frac": link / dot_avg / 1e9 / 770.0,
                     "traffic": None, "peak_source": "B200_PROFILING.md: measured peer copy 770 GB/s per direction per GPU",
                     "bytes_per_launch": link, "us_per_launch": dot_avg * 1e6, "launches_timed": len(dot_t),

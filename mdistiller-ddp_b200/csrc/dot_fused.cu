@@ -23,9 +23,11 @@
 // itself through a SYNC PAD, 64 uint32 of symmetric memory per rank:
 //   pad[0..15]   "start" flags, pad[r] written by rank r:  r's gradients are complete      (epoch number)
 //   pad[16..31]  "done" flags,  pad[16+r] written by rank r: r's writes to this rank's P have landed
-//   pad[32]      local count of finished thread blocks (ticket)
-// Start: block 0 releases its rank's start flag into every peer's pad; every block then waits (acquire, system
-// scope) until its OWN pad shows the current epoch from every rank -- the waiting reads are local.  End: each
+//   pad[32]      local count of finished thread blocks (ticket);  pad[33] local "go" word
+// Start: block 0 releases its rank's start flag into every peer's pad and waits (acquire, system scope, `world`
+// threads) until its OWN pad shows the current epoch from every rank -- the waiting reads are local; it then
+// publishes the epoch in the local "go" word, which one thread of every other block polls at device scope (so a
+// whole grid never hammers the system-scope flags).  End: each
 // block fences its peer / multicast stores at system scope and takes a ticket; the last block releases the
 // rank's done flag into every peer's pad and waits for every peer's done flag before it exits, so kernel
 // completion on this stream implies "all of P is final here".  Epochs only grow, a flag is never reset, and a
@@ -55,7 +57,7 @@ struct SyncPad {
     unsigned epoch;
     int rank;
 };
-constexpr int kPadDone = 16, kPadTicket = 32;
+constexpr int kPadDone = 16, kPadTicket = 32, kPadGo = 33;
 
 __device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
@@ -82,9 +84,23 @@ __device__ __forceinline__ void pad_wait(const unsigned *flag, unsigned epoch) {
 // every rank's inputs are complete (called by all threads of all blocks at kernel start)
 __device__ __forceinline__ void pad_start(const SyncPad &s, int world) {
     if (s.local == nullptr) return;
-    if (threadIdx.x < world) {
-        if (blockIdx.x == 0) st_release_sys(s.peer[threadIdx.x] + s.rank, s.epoch);
-        pad_wait(s.local + threadIdx.x, s.epoch);
+    if (blockIdx.x == 0) {
+        if (threadIdx.x < world) {
+            st_release_sys(s.peer[threadIdx.x] + s.rank, s.epoch);
+            pad_wait(s.local + threadIdx.x, s.epoch);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0)
+            asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(s.local + kPadGo), "r"(s.epoch) : "memory");
+    } else if (threadIdx.x == 0) {
+        const unsigned long long t0 = global_ns();
+        unsigned v;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(s.local + kPadGo) : "memory");
+            if ((int)(v - s.epoch) >= 0) break;
+            __nanosleep(200);
+            if (global_ns() - t0 > 25ull * 1000 * 1000 * 1000) __trap();
+        } while (true);
     }
     __syncthreads();
 }

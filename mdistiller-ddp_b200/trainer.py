@@ -73,7 +73,11 @@ class TailStepMixin:
             return None
         world = dist.get_world_size()
         mode = resolve_comm_mode(self.comm_mode, world)
-        fusable = self.trainer_kind == "dot" or self.__dict__.get("_base_solver", "SGD") == "SGD"
+        # the fused NVLink step exists for DOT and for the base trainer's momentum SGD; "auto" picks it for DOT
+        # only: measured on 8 B200s (profiles/r2_n8_*), it wins on the DOT trainer (3 collectives -> 1 kernel:
+        # +18 % images/s on KD+DOT ResNet32x4->ResNet8x4) and loses to two NCCL launches on the base trainer
+        fusable = self.trainer_kind == "dot" or (self.comm_mode != "auto" and
+                                                 self.__dict__.get("_base_solver", "SGD") == "SGD")
         if mode != "nccl" and world > 1 and fusable:
             try:
                 comm = SymmetricShardComm(fuse_kd=mode.startswith("fused_kd"), use_multicast=not mode.endswith("p2p"),
