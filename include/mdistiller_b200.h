@@ -255,7 +255,8 @@ MDB200_API int mdb200_metrics_record(const float *logits, const int64_t *target,
  * (mdistiller/engine/trainer.py:86-91) and stepped at trainer.py:321.
  * v may be NULL when momentum == 0.  grad_scale_dev (may be NULL) points at one float on
  * the device that also multiplies the gradient -- the clipping coefficient of
- * mdb200_clip_coefficient.  20 algorithmic bytes per element.
+ * mdb200_clip_coefficient or the unscale factor of mdb200_amp_step_scale; a NEGATIVE value
+ * means "skip": the kernel returns without touching p or v.  20 algorithmic bytes per element.
  */
 MDB200_API int mdb200_sgd_step(float *p, const float *g, float *v, int64_t n,
                     float lr, float momentum, float weight_decay, float dampening,
@@ -288,6 +289,22 @@ MDB200_API int mdb200_adam_step(float *p, const float *g, float *m, float *v, in
 MDB200_API int mdb200_sum_squares(const float *x, int64_t n, float scale, double *out,
                     void *workspace, size_t workspace_bytes, void *stream);
 MDB200_API int mdb200_clip_coefficient(const double *total_sumsq, float max_norm, float *coef, void *stream);
+
+/*
+ * Mixed-precision loss scaling decided on the device: the AMP branch of BaseTrainer.backward_loss
+ * (mdistiller/engine/trainer.py:304-313: GradScaler.scale / unscale_ / clip_grad_norm_ / step / update) without a
+ * host read of the overflow flag and without a pass that rewrites the gradients.
+ *   total_sumsq     sum of squares of the SCALED (and rank-averaged) gradient from mdb200_sum_squares, all-reduced
+ *                   over ranks by the host code; non-finite exactly when some gradient element is inf or nan
+ *   scale, growth_tracker   the scaler's state on the device, updated in place (GradScaler.update: x backoff_factor
+ *                   after an overflow, x growth_factor after growth_interval clean steps in a row)
+ *   max_norm        SOLVER.GRAD_CLIP on the unscaled gradient, 0 = no clipping
+ *   coef            out: 1/scale (x clipping coefficient), to be passed as grad_scale_dev of mdb200_sgd_step /
+ *                   mdb200_adam_step; NEGATIVE after an overflow, which those kernels take as "skip this update"
+ */
+MDB200_API int mdb200_amp_step_scale(const double *total_sumsq, float *scale, int *growth_tracker,
+                    float growth_factor, float backoff_factor, int growth_interval, float max_norm,
+                    float *coef, void *stream);
 
 #ifdef __cplusplus
 }

@@ -12,6 +12,7 @@ from . import ops  # noqa: F401
 from .losses import dkd_loss, kd_loss, distill_tail, TailResult  # noqa: F401
 from .distillers import Distiller, DKD, KD  # noqa: F401
 from .optim import DistillationOrientedTrainer, FlatAdam, FlatSGD  # noqa: F401
+from .amp import DeviceLossScaler  # noqa: F401
 from .comm import ShardComm  # noqa: F401
 from .flat import FlatSpace  # noqa: F401
 from .trainer import TailStepMixin, StandaloneTrainer, new_train_meters, silence_ddp_reducer  # noqa: F401
@@ -23,5 +24,5 @@ __all__ = [
     "dkd_loss", "kd_loss", "distill_tail", "TailResult", "Distiller", "DKD", "KD",
     "DistillationOrientedTrainer", "FlatSGD", "FlatAdam", "ShardComm", "FlatSpace", "TailStepMixin",
     "StandaloneTrainer", "new_train_meters", "silence_ddp_reducer", "install", "uninstall", "distiller_dict",
-    "build_library", "LIB_PATH", "ops",
+    "build_library", "LIB_PATH", "ops", "DeviceLossScaler",
 ]

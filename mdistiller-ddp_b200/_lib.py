@@ -47,6 +47,7 @@ SIGNATURES = {
     "mdb200_metrics_record": (_int, [_ptr, _ptr, _i64, _i64, _i64, _ptr, _ptr, _ptr, _ptr]),
     "mdb200_sum_squares": (_int, [_ptr, _i64, _f32, _ptr, _ptr, C.c_size_t, _ptr]),
     "mdb200_clip_coefficient": (_int, [_ptr, _f32, _ptr, _ptr]),
+    "mdb200_amp_step_scale": (_int, [_ptr, _ptr, _ptr, _f32, _f32, _int, _f32, _ptr, _ptr]),
 }
 
 _lock = threading.Lock()

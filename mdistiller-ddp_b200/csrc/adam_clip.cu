@@ -35,7 +35,9 @@ constexpr int kAdamThreads = 256;
 __global__ void __launch_bounds__(kAdamThreads) adam_vec4(float4 *__restrict__ p, const float4 *__restrict__ g,
                                                           float4 *__restrict__ m, float4 *__restrict__ v, long long n4,
                                                           const AdamCoef c, const float *__restrict__ gs_dev) {
-    const float gs = c.gscale * (gs_dev ? __ldg(gs_dev) : 1.0f);
+    const float gs_f = gs_dev ? __ldg(gs_dev) : 1.0f;
+    if (gs_f < 0.f) return;                  // AMP overflow verdict: skip the whole update (mdb200_amp_step_scale)
+    const float gs = c.gscale * gs_f;
     const long long tile = 2LL * kAdamThreads;
     for (long long t0 = (long long)blockIdx.x * tile; t0 < n4; t0 += (long long)gridDim.x * tile) {
         float4 P[2], G[2], M[2], V[2];
@@ -67,7 +69,9 @@ __global__ void __launch_bounds__(kAdamThreads) adam_vec4(float4 *__restrict__ p
 
 __global__ void __launch_bounds__(kAdamThreads) adam_scalar(float *p, const float *g, float *m, float *v, long long n,
                                                             const AdamCoef c, const float *gs_dev) {
-    const float gs = c.gscale * (gs_dev ? __ldg(gs_dev) : 1.0f);
+    const float gs_f = gs_dev ? __ldg(gs_dev) : 1.0f;
+    if (gs_f < 0.f) return;                  // AMP overflow verdict: skip the whole update (mdb200_amp_step_scale)
+    const float gs = c.gscale * gs_f;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
         float P = p[i], M = m[i], V = v[i];
         adam_one(P, g[i], M, V, c, gs);
@@ -138,9 +142,46 @@ __global__ void clip_coefficient_kernel(const double *total_sumsq, float max_nor
     *coef = fminf(max_norm / (norm + 1e-6f), 1.0f);
 }
 
+// One thread: everything torch's GradScaler decides per step (unscale_ + found_inf + update) plus the clipping
+// coefficient, from the fp64 sum of squares of the SCALED gradient.  fp64 sums of fp32 squares cannot overflow, so the
+// sum is non-finite exactly when some gradient element is inf or nan.
+__global__ void amp_step_scale_kernel(const double *total_sumsq, float *scale, int *growth_tracker, float growth_factor,
+                                      float backoff_factor, int growth_interval, float max_norm, float *coef) {
+    const double ss = *total_sumsq;
+    const float sc = *scale;
+    if (!isfinite(ss)) {                     // overflow: skip this step, back the scale off
+        *coef = -1.0f;
+        *scale = sc * backoff_factor;
+        *growth_tracker = 0;
+        return;
+    }
+    const float inv = (float)(1.0 / (double)sc);          // GradScaler: scale.double().reciprocal().float()
+    float c = inv;
+    if (max_norm > 0.f) {
+        const float norm = (float)sqrt(ss) * inv;         // norm of the unscaled, rank-averaged gradient
+        c *= fminf(max_norm / (norm + 1e-6f), 1.0f);
+    }
+    *coef = c;
+    int t = *growth_tracker + 1;
+    if (t == growth_interval) {
+        *scale = sc * growth_factor;
+        t = 0;
+    }
+    *growth_tracker = t;
+}
+
 }  // namespace mdb200
 
 using namespace mdb200;
+
+extern "C" int mdb200_amp_step_scale(const double *total_sumsq, float *scale, int *growth_tracker, float growth_factor,
+                                     float backoff_factor, int growth_interval, float max_norm, float *coef, void *stream) {
+    if (!total_sumsq || !scale || !growth_tracker || !coef) return MDB200_EINVAL;
+    if (!(growth_factor >= 1.f) || !(backoff_factor > 0.f && backoff_factor <= 1.f) || growth_interval < 1) return MDB200_EINVAL;
+    amp_step_scale_kernel<<<1, 1, 0, reinterpret_cast<cudaStream_t>(stream)>>>(total_sumsq, scale, growth_tracker, growth_factor,
+                                                                           backoff_factor, growth_interval, max_norm, coef);
+    return (int)cudaGetLastError();
+}
 
 extern "C" int mdb200_adam_step(float *p, const float *g, float *m, float *v, int64_t n, float lr, double beta1,
                                 double beta2, float eps, float weight_decay, int decoupled, int64_t step,

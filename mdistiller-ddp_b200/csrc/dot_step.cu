@@ -50,7 +50,11 @@ __global__ void __launch_bounds__(kStepThreads) flat_step_vec4(float4 *__restric
                                                                const float4 *__restrict__ gk, float4 *__restrict__ vt,
                                                                float4 *__restrict__ vk, long long n4, StepCoef c,
                                                                const float *__restrict__ gs_dev) {
-    if (gs_dev) c.gscale *= __ldg(gs_dev);   // device-side factor (gradient-clipping coefficient)
+    if (gs_dev) {                            // device-side factor: clipping coefficient / AMP unscale ...
+        const float f = __ldg(gs_dev);
+        if (f < 0.f) return;                 // ... or the AMP overflow verdict: skip the whole update (mdb200_amp_step_scale)
+        c.gscale *= f;
+    }
     const long long tile = (long long)kStepThreads * kStepUnroll;
     const bool use_vt = TASK && !c.bypass_task;
     for (long long t0 = (long long)blockIdx.x * tile; t0 < n4; t0 += (long long)gridDim.x * tile) {
@@ -86,7 +90,11 @@ __global__ void __launch_bounds__(kStepThreads) flat_step_vec4(float4 *__restric
 template <bool TASK, bool KD>
 __global__ void __launch_bounds__(kStepThreads) flat_step_scalar(float *p, const float *gt, const float *gk, float *vt,
                                                                  float *vk, long long n, StepCoef c, const float *gs_dev) {
-    if (gs_dev) c.gscale *= __ldg(gs_dev);
+    if (gs_dev) {
+        const float f = __ldg(gs_dev);
+        if (f < 0.f) return;
+        c.gscale *= f;
+    }
     const bool use_vt = TASK && !c.bypass_task;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
         float P = p[i], GT = TASK ? gt[i] : 0.f, GK = KD ? gk[i] : 0.f;

@@ -202,6 +202,28 @@ def clip_coefficient(total_sumsq: torch.Tensor, max_norm: float, out: Optional[t
     return out
 
 
+def amp_step_scale(total_sumsq: torch.Tensor, scale: torch.Tensor, growth_tracker: torch.Tensor, *, growth_factor: float,
+                   backoff_factor: float, growth_interval: int, max_norm: float = 0.0,
+                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """GradScaler's per-step decisions on the device (see mdb200_amp_step_scale): returns the device scalar to pass as
+    ``grad_scale_dev`` (1/scale x clipping coefficient, negative = skip the update); ``scale`` and
+    ``growth_tracker`` are updated in place."""
+    global launch_count
+    lib = _lib.load()
+    if not (total_sumsq.is_cuda and total_sumsq.dtype == torch.float64 and scale.is_cuda and scale.dtype == torch.float32
+            and growth_tracker.is_cuda and growth_tracker.dtype == torch.int32):
+        raise TypeError("total_sumsq: CUDA float64, scale: CUDA float32, growth_tracker: CUDA int32")
+    if out is None:
+        out = torch.empty(1, dtype=torch.float32, device=scale.device)
+    with torch.cuda.device(scale.device):
+        rc = lib.mdb200_amp_step_scale(total_sumsq.data_ptr(), scale.data_ptr(), growth_tracker.data_ptr(),
+                                       growth_factor, backoff_factor, int(growth_interval), float(max_norm or 0.0),
+                                       out.data_ptr(), _stream_ptr(scale.device))
+    _lib.check(rc, "mdb200_amp_step_scale")
+    launch_count += 1
+    return out
+
+
 def metrics_record(logits: torch.Tensor, target: torch.Tensor, loss_ce: Optional[torch.Tensor],
                    loss_kd: Optional[torch.Tensor]) -> torch.Tensor:
     """5 floats on the device: {loss_ce, loss_kd, top-1 hits, top-5 hits, rows} -- one launch."""

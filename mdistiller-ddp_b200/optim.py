@@ -176,6 +176,19 @@ class _FlatOptimizer(Optimizer):
         self._comm.all_reduce_sum(sumsq)
         return self._k.clip_coefficient(sumsq, float(max_norm))
 
+    # mixed precision: set by the trainer (a DeviceLossScaler); the bucket then holds SCALED gradients
+    loss_scaler = None
+
+    def _step_multiplier(self, bucket: torch.Tensor, max_norm: float) -> Optional[torch.Tensor]:
+        """Device scalar that multiplies the shard's gradient inside the step kernel: the clipping coefficient,
+        and under AMP 1/scale (x clipping) -- or a negative value, which makes the kernel skip the update
+        (the scaler's overflow verdict; identical on every rank because it comes from the all-reduced norm)."""
+        if self.loss_scaler is None:
+            return self._clip_coefficient(bucket, max_norm)
+        sumsq = self._k.sum_squares(self._space.shard(bucket), scale=1.0 / self._comm.world_size)
+        self._comm.all_reduce_sum(sumsq)
+        return self.loss_scaler.verdict(sumsq, float(max_norm or 0.0))
+
     @property
     def flat_params(self) -> torch.Tensor:
         return self._space.flat
@@ -446,7 +459,7 @@ class FlatSGD(_FlatOptimizer):
         # when every parameter has a gradient with the same first-step flag -- a GLOBAL property, so all ranks
         # agree -- and no clipping norm has to be formed from the reduced gradient first
         fused = (getattr(comm, "fused", False) and comm.world_size > 1 and not (self.max_grad_norm and self.max_grad_norm > 0)
-                 and modes[0][0] == _TASK and all(m == modes[0] for m in modes))
+                 and self.loss_scaler is None and modes[0][0] == _TASK and all(m == modes[0] for m in modes))
         if fused:
             p, g = sp.flat, self._buckets["grad"]
             (p_mc, p_peers), (g_mc, g_peers) = comm.addresses(p), comm.addresses(g)
@@ -466,7 +479,7 @@ class FlatSGD(_FlatOptimizer):
             work = comm.reduce_scatter_sum(self._buckets["grad"], async_op=True)
             if work is not None:
                 work.wait()
-            clip = self._clip_coefficient(self._buckets["grad"], self.max_grad_norm)
+            clip = self._step_multiplier(self._buckets["grad"], self.max_grad_norm)
             for lo, hi, (_, first, _) in self._runs(modes):
                 a, b = lo - sp.shard_lo, hi - sp.shard_lo
                 self._k.sgd_step(sp.flat[lo:hi], self._buckets["grad"][lo:hi],
@@ -475,10 +488,17 @@ class FlatSGD(_FlatOptimizer):
                                  dampening=group["dampening"], grad_scale=1.0 / comm.world_size,
                                  first_step=first, grad_scale_dev=clip)
             comm.all_gather(sp.flat)
-        if momentum != 0:
+        if momentum != 0 and self.loss_scaler is None:
             for i, t in enumerate(members):
                 if t:
                     self._has_v[i] = True
+        elif momentum != 0 and not all(self._has_v):
+            # under AMP the very first update may be skipped on the device; "buffer exists" is only certain once a
+            # step has gone through, so the first-step flag is kept until the host has seen one clean verdict
+            if float(self.loss_scaler.coef.item()) > 0:          # a host read, on the first step(s) only
+                for i, t in enumerate(members):
+                    if t:
+                        self._has_v[i] = True
         self._n_steps += 1
         self._snapshot = None
         return loss
@@ -526,6 +546,7 @@ class FlatAdam(_FlatOptimizer):
         self._m = self._space.new_shard_buffer()
         self._v = self._space.new_shard_buffer()
         self._steps = [0] * len(self._space.params)     # per parameter, like torch's state['step']
+        self._amp_pending = None
         self.max_grad_norm = 0.0
 
     @torch.no_grad()
@@ -539,7 +560,16 @@ class FlatAdam(_FlatOptimizer):
         work = self._comm.reduce_scatter_sum(self._buckets["grad"], async_op=True)
         if work is not None:
             work.wait()
-        clip = self._clip_coefficient(self._buckets["grad"], self.max_grad_norm)
+        # the previous step's overflow verdict, copied to pinned memory back then: a skipped update must not count as
+        # an Adam step (GradScaler would not have called optimizer.step() at all)
+        self._settle_amp()
+        clip = self._step_multiplier(self._buckets["grad"], self.max_grad_norm)
+        if self.loss_scaler is not None:
+            host = torch.empty(1, dtype=torch.float32, pin_memory=True)
+            host.copy_(clip, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record()
+            self._amp_pending = (done, host, [i for i, t in enumerate(members) if t])
         for i, t in enumerate(members):
             if t:
                 self._steps[i] += 1
@@ -557,7 +587,17 @@ class FlatAdam(_FlatOptimizer):
         self._snapshot = None
         return loss
 
+    def _settle_amp(self):
+        if self._amp_pending is not None:
+            done, host, who = self._amp_pending
+            done.synchronize()
+            if float(host.item()) < 0:
+                for i in who:
+                    self._steps[i] -= 1
+            self._amp_pending = None
+
     def _state_pairs(self):
+        self._settle_amp()
         has = [n > 0 for n in self._steps]
         return (("exp_avg", self._m, has), ("exp_avg_sq", self._v, list(has)))
 

@@ -24,6 +24,7 @@ import torch.distributed as dist
 
 from . import ops
 from .comm import ShardComm, SymmetricShardComm
+from .amp import DeviceLossScaler
 from .optim import DistillationOrientedTrainer, FlatAdam, FlatSGD
 
 
@@ -108,11 +109,13 @@ class TailStepMixin:
                 momentum=cfg.SOLVER.SGD.MOMENTUM - cfg.SOLVER.DOT.DELTA,
                 momentum_kd=cfg.SOLVER.SGD.MOMENTUM + cfg.SOLVER.DOT.DELTA,
                 weight_decay=cfg.SOLVER.WEIGHT_DECAY, comm=comm))
-        # AMP (trainer.py:79-80, 268, 304-313): autocast forward + torch's GradScaler around our step; the
-        # scaled loss then has to go through autograd, so the pre-combined gradient shortcut is off
+        # AMP (trainer.py:79-80, 268, 304-313): autocast forward; the loss scale lives on the device and its
+        # unscale / overflow check / update are folded into the flat step (amp.DeviceLossScaler)
         self.use_amp = bool(cfg.EXPERIMENT.AMP)
-        self.amp_scaler = torch.amp.GradScaler("cuda") if self.use_amp else None
-        core.combined_tail = not self.use_amp     # one gradient buffer: the base trainer sums the losses anyway
+        # (kept on the optimizer: the reference's BaseTrainer.__init__ assigns its own GradScaler to self.amp_scaler
+        #  right after this call, trainer.py:79-80 -- it is simply never used on this path)
+        loss_scaler = DeviceLossScaler(params[0].device) if self.use_amp else None
+        core.combined_tail = True                 # one gradient buffer: the base trainer sums the losses anyway
         kind = cfg.SOLVER.TYPE
         if kind == "SGD":
             opt = FlatSGD(params, lr=cfg.SOLVER.LR, momentum=cfg.SOLVER.SGD.MOMENTUM,
@@ -124,6 +127,7 @@ class TailStepMixin:
         else:
             raise NotImplementedError(kind)
         opt.max_grad_norm = float(getattr(cfg.SOLVER, "GRAD_CLIP", 0.0) or 0.0)   # clip inside step(), on the shard
+        opt.loss_scaler = loss_scaler
         return _trust(opt)
 
     # ---------------------------------------------------------------- one iteration
@@ -195,16 +199,14 @@ class TailStepMixin:
             with torch.autocast("cuda"):
                 preds, losses = self.distiller(image=image, target=target, epoch=epoch)
             tail = getattr(core, "last_tail", None)
-            scaler = self.amp_scaler
-            scaler.scale(sum(losses.values())).backward()
-            scaler.unscale_(opt)      # in place on the bucket views; clipping itself happens inside opt.step()
-            if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-                # DDP's all-reduce would spread an inf/nan to every rank; the sharded step must agree on
-                # skipping before anybody enters the reduce-scatter
-                for found in scaler._per_optimizer_states[id(opt)]["found_inf_per_device"].values():
-                    dist.all_reduce(found, op=dist.ReduceOp.MAX)
-            scaler.step(opt)
-            scaler.update()
+            scaler = opt.loss_scaler
+            if tail is not None and tail.combined:
+                # GradScaler.scale(loss).backward(): seed the backward with (dloss/dlogits) x scale, in the logits' dtype
+                seed = scaler.scale_gradient(tail.grad_kd).to(tail.logits.dtype)
+                torch.autograd.backward([tail.logits], [seed])
+            else:
+                (sum(losses.values()) * scaler.scale.squeeze(0)).backward()
+            opt.step()        # unscale, overflow check, clipping and the scaler's update happen inside, on the device
         else:
             opt.zero_grad()
             preds, losses = self.distiller(image=image, target=target, epoch=epoch)

@@ -338,9 +338,10 @@ def test_generic_autograd_protocol_equals_seeded_backward(b200):
 
 
 def test_base_trainer_amp_branch(b200):
-    """EXPERIMENT.AMP with the base trainer (trainer.py:268, 304-313): autocast forward, torch's GradScaler
-    around the flat step.  fp16 backbones make exact parity meaningless; check the mechanics instead:
-    finite losses close to the fp32 run, parameters move, and an overflowing scale skips the step."""
+    """EXPERIMENT.AMP with the base trainer (trainer.py:268, 304-313): autocast forward, loss scale kept on the
+    device and folded into the flat step.  fp16 backbones make exact parity meaningless here (the scaler's
+    arithmetic is pinned to torch's GradScaler in the next test); check the mechanics: finite losses close to the
+    fp32 run, parameters move, and an overflowing scale skips the step and backs off."""
     from mdistiller_ddp_b200 import workloads as W
     import copy
     torch.manual_seed(4)
@@ -350,7 +351,7 @@ def test_base_trainer_amp_branch(b200):
     cfg.EXPERIMENT.AMP = True
     cfg.SOLVER.GRAD_CLIP = 5.0
     amp_tr = b200.StandaloneTrainer(b200.DKD(student, teacher, cfg).cuda().train(), cfg, kind="base")
-    assert amp_tr.use_amp and amp_tr.amp_scaler is not None and amp_tr.optimizer.max_grad_norm == 5.0
+    assert amp_tr.use_amp and amp_tr.optimizer.loss_scaler is not None and amp_tr.optimizer.max_grad_norm == 5.0
     cfg32 = W.default_cfg("cifar_res32x4_res8x4_dkd_base")
     cfg32.SOLVER.GRAD_CLIP = 5.0
     ref_tr = b200.StandaloneTrainer(b200.DKD(s32, t32, cfg32).cuda().train(), cfg32, kind="base")
@@ -365,11 +366,55 @@ def test_base_trainer_amp_branch(b200):
     assert not torch.equal(before, after)
     assert oracle.max_rel_err(after, ref_tr.optimizer.flat_params) <= 5e-3
     # overflow: a scale far beyond fp16 range -> inf gradients -> GradScaler skips our step and backs off
-    amp_tr.amp_scaler = torch.amp.GradScaler("cuda", init_scale=2.0 ** 120)
+    amp_tr.optimizer.loss_scaler = b200.DeviceLossScaler(after.device, init_scale=2.0 ** 120)
     image, target, _ = W.synthetic_batch(32, 32, 100, seed=50)
     amp_tr.tail_step(image.cuda(), target.cuda(), 10)
     assert torch.equal(amp_tr.optimizer.flat_params, after)
-    assert amp_tr.amp_scaler.get_scale() == 2.0 ** 119
+    assert amp_tr.optimizer.loss_scaler.get_scale() == 2.0 ** 119
+
+
+@pytest.mark.parametrize("kind,clip", [("sgd", 0.0), ("sgd", 0.5), ("adamw", 0.5)])
+def test_device_loss_scaler_equals_torch_gradscaler(kind, clip, b200):
+    """Scaled gradients with an overflow at steps 4 and 5: FlatSGD / FlatAdam + DeviceLossScaler (unscale, inf check,
+    clipping and scale update inside the step, on the device) against torch.optim + torch.amp.GradScaler driven the way
+    BaseTrainer.backward_loss drives them (trainer.py:304-313).  Same scale after every step, same parameters."""
+    case = next(c for c in _cases.DOT_CASES if c.name == "sgd_cifar_small")
+    mk = lambda: [torch.nn.Parameter(p.clone().cuda()) for p in _cases.make_params(case)]
+    ours_p, ref_p = mk(), mk()
+    if kind == "sgd":
+        ours = b200.FlatSGD(ours_p, lr=case.lr, momentum=case.momentum, weight_decay=case.wd)
+        ref = torch.optim.SGD(ref_p, lr=case.lr, momentum=case.momentum, weight_decay=case.wd)
+    else:
+        ours = b200.FlatAdam(ours_p, lr=1e-3, betas=_cases.ADAM_BETAS, eps=_cases.ADAM_EPS, weight_decay=5e-2, decoupled=True)
+        ref = torch.optim.AdamW(ref_p, lr=1e-3, betas=_cases.ADAM_BETAS, eps=_cases.ADAM_EPS, weight_decay=5e-2)
+    ours.max_grad_norm = clip
+    ours.loss_scaler = b200.DeviceLossScaler(ours_p[0].device, init_scale=1024.0, growth_interval=3)
+    scaler = torch.amp.GradScaler("cuda", init_scale=1024.0, growth_interval=3)
+    scaler.scale(torch.zeros(1, device="cuda"))                      # materialises its scale tensor
+    shapes = [p.shape for p in ours_p]
+    for step in range(14):
+        _, task = _cases.make_grads(case, step, shapes)
+        scale = scaler.get_scale()
+        assert ours.loss_scaler.get_scale() == scale, step
+        grads = [(g * scale).cuda() for g in task]
+        if step in (4, 5):
+            grads[2][0] = float("inf") if step == 4 else float("nan")
+        ours.zero_grad()
+        ref.zero_grad()
+        for p, q, g in zip(ours_p, ref_p, grads):
+            p.grad, q.grad = g.clone(), g.clone()
+        ours.step()
+        if clip > 0:
+            scaler.unscale_(ref)
+            torch.nn.utils.clip_grad_norm_(ref_p, clip)
+        scaler.step(ref)
+        scaler.update()
+    assert ours.loss_scaler.get_scale() == scaler.get_scale() == 1024.0 * 0.25 * 2 ** 2   # 2 back-offs, then growth every 3 clean steps
+    for p, q in zip(ours_p, ref_p):
+        assert oracle.max_rel_err(p, q) <= TOL
+    if kind != "sgd":
+        sd = ours.state_dict()["state"]
+        assert float(sd[0]["step"]) == 12.0 == float(ref.state[ref_p[0]]["step"])     # the two skipped updates do not count
 
 
 def test_lagged_metrics_account_every_iteration(b200):
