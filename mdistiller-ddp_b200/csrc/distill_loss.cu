@@ -210,7 +210,8 @@ __device__ __forceinline__ void cta_reduce_and_publish(const LossArgs &A, double
     if (lane == 0) {
         A.loss_out[0] = (float)(s_kd * A.l_kd);
         A.loss_out[1] = (float)(s_ce * A.l_ce);
-        *A.ticket = 0u;  // ready for the next launch on this scratch
+        A.ticket[1] = 0u;  // the lean kernels' tile counter
+        *A.ticket = 0u;    // ready for the next launch on this scratch
     }
 }
 
@@ -420,10 +421,18 @@ __global__ void __launch_bounds__(kLossThreads, (NV >= 16 ? 1 : 2)) loss_rows_in
 //   * CFIX: the class count as a compile-time constant for the two standard datasets (100, 1000), so the
 //     tail guards, the row offsets inside the tile and the vector count fold away;
 //   * MINB: resident blocks per SM asked of the register allocator.
+// Measured and dropped (B200, profiles/r2_loss_ab.txt): 3-4 resident blocks per SM (80 / 64 registers: spills, no
+// gain -- ncu shows the SMs streaming at 6.4 TB/s while they are active, the time goes to the launch ramp and the
+// drain); 8 lanes per row; and drawing tiles from an atomic counter instead of the fixed stride (+20 %: 2 368 warps
+// on one counter cost more than the uneven last round they remove).
 // Arithmetic and summation order are those of loss_rows_in_registers; only the label column's gradient is
 // formed from scalars (same formula).
 // ---------------------------------------------------------------------------------------
-template <int LPR, int NV, int CFIX, bool DKD, int CE, bool SPLIT, int MINB>
+//   * DYN: warps take their row tiles from a counter in the scratch header instead of a fixed stride, one tile ahead
+//     of the one they work on (the round trip of the atomic is hidden behind a whole tile): SMs that run ahead
+//     take more tiles, so the grid drains together instead of waiting for the blocks that drew one tile more
+//     (ncu r2a: SM-active cycles 21 K ... 32 K around a 24 K mean with the fixed stride).
+template <int LPR, int NV, int CFIX, bool DKD, int CE, bool SPLIT, int MINB, bool DYN = false>
 __global__ void __launch_bounds__(kLossThreads, MINB) loss_rows_lean(const LossArgs A) {
     constexpr int GPW = 32 / LPR;  // rows per warp
     const int C = CFIX ? CFIX : (int)A.classes;
@@ -452,6 +461,20 @@ __global__ void __launch_bounds__(kLossThreads, MINB) loss_rows_lean(const LossA
         mbar_init_fence();
     }
     __syncthreads();
+    // DYN: tile numbers come from the counter next to the ticket (both are zero between launches); the first
+    // gridDim.x * kLossWarps tiles are the warps' own, so only later ones cost an atomic
+    unsigned *tile_counter = A.ticket + 1;
+    const long long n_tiles = (A.rows + GPW - 1) / GPW;
+    const long long own = (long long)blockIdx.x * kLossWarps + warp, all_warps = (long long)gridDim.x * kLossWarps;
+    unsigned t_pending = 0;                    // lane 0: the counter value requested one tile ago (not waited for yet)
+    auto request_tile = [&]() {
+        if (lane == 0) t_pending = atomicAdd(tile_counter, 1u);
+    };
+    auto resolve_tile = [&]() -> long long {   // first use of the atomic's result: every lane gets the same answer
+        const unsigned t = __shfl_sync(0xffffffffu, t_pending, 0);
+        return ((long long)t + all_warps) * GPW;
+    };
+    if (DYN && own < n_tiles) request_tile();
     long long g_next = -1;
     if (first < A.rows) {
         if (lane == 0) issue_tile(first);
@@ -462,7 +485,8 @@ __global__ void __launch_bounds__(kLossThreads, MINB) loss_rows_lean(const LossA
     const float4 *pt = reinterpret_cast<const float4 *>(tile_t + grp * C) + sub;
     constexpr float kLog2e = 1.4426950408889634f;
 
-    for (long long base = first; base < A.rows; base += sweep) {
+    long long nb_carry = 0;
+    for (long long base = first; base < A.rows; base = DYN ? nb_carry : base + sweep) {
         const long long row = base + grp;
         const bool live = row < A.rows;
         const long long r = live ? row : A.rows - 1;
@@ -494,13 +518,15 @@ __global__ void __launch_bounds__(kLossThreads, MINB) loss_rows_lean(const LossA
             }
         }
         __syncwarp();                      // every lane has its copy: the tile may be overwritten
-        const long long nb = base + sweep;
+        const long long nb = DYN ? resolve_tile() : base + sweep;
+        nb_carry = nb;
         if (nb < A.rows) {
             if (lane == 0) {
                 fence_proxy_async_smem();
                 issue_tile(nb);
             }
             if (DKD || CE != 0) g_next = A.target[nb + grp < A.rows ? nb + grp : A.rows - 1];
+            if (DYN) request_tile();               // the tile after next: its number arrives while this one is computed
         }
 
         // pass 1: maxima of the kept classes
@@ -780,11 +806,11 @@ static cudaError_t launch_staged(const LossArgs &A, const LaunchCtx &ctx) {
     return cudaGetLastError();
 }
 
-template <int LPR, int NV, int CFIX, bool DKD, int CE, bool SPLIT, int MINB>
+template <int LPR, int NV, int CFIX, bool DKD, int CE, bool SPLIT, int MINB, bool DYN = false>
 static cudaError_t launch_lean(const LossArgs &A, const LaunchCtx &ctx) {
     constexpr int GPW = 32 / LPR;
     constexpr int rows_per_cta = kLossWarps * GPW;
-    auto kernel = loss_rows_lean<LPR, NV, CFIX, DKD, CE, SPLIT, MINB>;
+    auto kernel = loss_rows_lean<LPR, NV, CFIX, DKD, CE, SPLIT, MINB, DYN>;
     const size_t region = (2 * (size_t)GPW * A.classes * sizeof(float) + 127) & ~(size_t)127;
     const size_t smem = 128 + kLossWarps * region;
     static PerDeviceInt configured, occ_cache, occ_smem;
@@ -817,11 +843,15 @@ static cudaError_t launch_shape(const LossArgs &A, bool vec_ok, const LaunchCtx 
         // 1000-class rows up to 32 K rows; the general-T cross entropy next to DKD keeps a third register row and
         // spills there, so that one combination stays on the round-1 kernel
         const int lean = lean_variant();
-        const bool third_row = DKD && CE == 2;
-        if (lean >= 1 && A.classes == 100 && !third_row) return launch_lean<4, 7, 100, DKD, CE, SPLIT, 2>(A, ctx);
-        if (lean >= 1 && A.classes == 1000 && A.rows <= 32768 && CE != 2) return launch_lean<32, 8, 1000, DKD, CE, SPLIT, 2>(A, ctx);
-        if (lean >= 1 && nvec <= 28 && !third_row) return launch_lean<4, 7, 0, DKD, CE, SPLIT, 2>(A, ctx);
-        if (lean >= 1 && nvec <= 32 && !third_row) return launch_lean<8, 4, 0, DKD, CE, SPLIT, 2>(A, ctx);
+        constexpr bool third_row = DKD && CE == 2;
+        if constexpr (!third_row) {
+            if (lean >= 1 && A.classes == 100) return launch_lean<4, 7, 100, DKD, CE, SPLIT, 2>(A, ctx);
+            if (lean >= 1 && nvec <= 28) return launch_lean<4, 7, 0, DKD, CE, SPLIT, 2>(A, ctx);
+            if (lean >= 1 && nvec <= 32) return launch_lean<8, 4, 0, DKD, CE, SPLIT, 2>(A, ctx);
+        }
+        if constexpr (CE != 2) {
+            if (lean >= 1 && A.classes == 1000 && A.rows <= 32768) return launch_lean<32, 8, 1000, DKD, CE, SPLIT, 2>(A, ctx);
+        }
         if (nvec <= 28) return launch_staged<4, 7, DKD, CE, SPLIT>(A, ctx);
         if (nvec <= 32) return launch_staged<8, 4, DKD, CE, SPLIT>(A, ctx);
         if (nvec > 128 && nvec <= 256 && A.rows <= 32768) return launch_staged<32, 8, DKD, CE, SPLIT>(A, ctx);

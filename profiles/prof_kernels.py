@@ -52,11 +52,20 @@ def adam(n):
     torch.cuda.synchronize()
 
 
+def kd(B, C, T):
+    zs, zt = torch.randn(B, C, device=dev) * 3, torch.randn(B, C, device=dev) * 3
+    gk, lo = torch.empty_like(zs), torch.empty(2, device=dev)
+    for _ in range(reps):
+        ops.distill_loss(zs, zt, None, kind=ops.LOSS_KD, temperature=T, grad_kd=gk, loss_out=lo)
+    torch.cuda.synchronize()
+
+
 loss(65536, 1000, 1.0, 0.5, ops.CE_NONE)
 loss(65536, 1000, 1.0, 0.5, ops.CE_SPLIT)
-loss(65536, 100, 4.0, 8.0, ops.CE_NONE)
+loss(65536, 100, 4.0, 8.0, ops.CE_NONE)       # lean staged kernel <4,7,100>
+kd(65536, 100, 4.0)
 loss(256, 1000, 1.0, 0.5, ops.CE_SPLIT)
-loss(16384, 1000, 1.0, 0.5, ops.CE_NONE)      # TMA-staged path
+loss(16384, 1000, 1.0, 0.5, ops.CE_NONE)      # lean staged kernel <32,8,1000>
 dot(25_557_032)
 dot(11_689_512)
 adam(25_557_032)
