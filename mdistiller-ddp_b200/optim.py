@@ -189,6 +189,21 @@ class _FlatOptimizer(Optimizer):
         self._comm.all_reduce_sum(sumsq)
         return self.loss_scaler.verdict(sumsq, float(max_norm or 0.0))
 
+    # -- CUDA-graph replay of a whole step (graphstep.py): the Python side of step() does not run on a replay
+    _HOST_STATE = ("_n_steps", "_snapshot", "_snapshot_step", "_phase", "_kd_members", "_kd_work", "_kd_prereduced")
+
+    def host_state(self) -> dict:
+        return {k: getattr(self, k) for k in self._HOST_STATE if hasattr(self, k)}
+
+    def restore_host_state(self, saved: dict) -> None:
+        for k, v in saved.items():
+            setattr(self, k, v)
+
+    def note_replayed_step(self) -> None:
+        """A captured step has just been replayed: account for it like step() does."""
+        self._n_steps += 1
+        self._snapshot = None
+
     @property
     def flat_params(self) -> torch.Tensor:
         return self._space.flat

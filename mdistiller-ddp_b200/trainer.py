@@ -25,6 +25,7 @@ import torch.distributed as dist
 from . import ops
 from .comm import ShardComm, SymmetricShardComm
 from .amp import DeviceLossScaler
+from .graphstep import GraphedStep
 from .optim import DistillationOrientedTrainer, FlatAdam, FlatSGD
 
 
@@ -175,11 +176,21 @@ class TailStepMixin:
         return self.report(preds, target, losses, epoch, train_meters)
 
     def tail_step(self, image, target, epoch):
-        """forward -> backward(s) -> optimizer; returns (logits, {'loss_ce','loss_kd'}) on device."""
+        """forward -> backward(s) -> optimizer; returns (logits, {'loss_ce','loss_kd'}) on device.  Launch-bound
+        steady-state steps are replayed from a CUDA graph (graphstep.py), everything else runs eagerly."""
+        runner = self.__dict__.get("_graph_runner")
+        if runner is None:
+            runner = self._graph_runner = GraphedStep(self)
+        return runner.step(image, target, epoch)
+
+    def _eager_tail_step(self, image, target, epoch, graphed: bool = False):
         opt = self.optimizer
         core = _unwrap(self.distiller)
+        # inside a graph capture the DDP wrapper (whose reducer is switched off anyway) is bypassed: its forward
+        # hooks are host logic that must not be frozen into the graph
+        model = core if graphed else self.distiller
         if self.trainer_kind == "dot":
-            preds, losses = self.distiller(image=image, target=target, epoch=epoch)
+            preds, losses = model(image=image, target=target, epoch=epoch)
             tail = getattr(core, "last_tail", None)
             opt.zero_grad(set_to_none=True)
             if tail is not None and not tail.combined:
@@ -197,7 +208,7 @@ class TailStepMixin:
         elif getattr(self, "use_amp", False):
             opt.zero_grad()
             with torch.autocast("cuda"):
-                preds, losses = self.distiller(image=image, target=target, epoch=epoch)
+                preds, losses = model(image=image, target=target, epoch=epoch)
             tail = getattr(core, "last_tail", None)
             scaler = opt.loss_scaler
             if tail is not None and tail.combined:
@@ -209,7 +220,7 @@ class TailStepMixin:
             opt.step()        # unscale, overflow check, clipping and the scaler's update happen inside, on the device
         else:
             opt.zero_grad()
-            preds, losses = self.distiller(image=image, target=target, epoch=epoch)
+            preds, losses = model(image=image, target=target, epoch=epoch)
             tail = getattr(core, "last_tail", None)
             if tail is not None and tail.combined:
                 torch.autograd.backward([tail.logits], [tail.grad_kd])

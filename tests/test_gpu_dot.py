@@ -461,6 +461,48 @@ def test_epoch_end_settles_metrics_and_checkpoint_snapshot(b200):
         assert len(sd["state"]) == len(tr.optimizer.param_groups[0]["params"])
 
 
+@pytest.mark.parametrize("kind,distiller", [("dot", "KD"), ("base", "DKD")])
+def test_graph_replayed_steps_equal_eager_steps(kind, distiller, b200, monkeypatch):
+    """Launch-bound steps are replayed from a CUDA graph (graphstep.py).  Same nets, same batches: the trainer that
+    replays must end where the eager one ends, across a learning-rate change and an epoch change (both are launch
+    arguments baked into the graph, so each forces a fresh capture), and its metrics must account every iteration."""
+    from mdistiller_ddp_b200 import workloads as W, graphstep
+    import copy
+    torch.manual_seed(7)
+    teacher, student = W.TinyNet(100, 24), W.TinyNet(100, 16)
+    t2, s2 = copy.deepcopy(teacher), copy.deepcopy(student)
+    cfg = W.default_cfg("cifar_res32x4_res8x4_kd_dot" if kind == "dot" else "cifar_res32x4_res8x4_dkd_base")
+    cls = b200.KD if distiller == "KD" else b200.DKD
+    monkeypatch.setenv("MDB200_GRAPH", "0")
+    eager = b200.StandaloneTrainer(cls(student, teacher, cfg).cuda().train(), cfg, kind=kind)
+    eager.tail_step(*[t.cuda() for t in W.synthetic_batch(16, 32, 100, seed=0)[:2]], 1)
+    monkeypatch.setenv("MDB200_GRAPH", "1")
+    graphed = b200.StandaloneTrainer(cls(s2, t2, cfg).cuda().train(), cfg, kind=kind)
+    graphed.tail_step(*[t.cuda() for t in W.synthetic_batch(16, 32, 100, seed=0)[:2]], 1)
+    assert not eager._graph_runner.enabled and graphed._graph_runner.enabled
+    m1, m2 = b200.new_train_meters(), b200.new_train_meters()
+    for step in range(1, 16):
+        epoch = 1 if step < 11 else 2
+        if step == 8:
+            for tr in (eager, graphed):
+                tr.optimizer.param_groups[0]["lr"] *= 0.1          # what adjust_learning_rate does
+        batch = W.synthetic_batch(16, 32, 100, seed=step, pin=True)
+        eager.train_iter(batch, epoch, m1)
+        graphed.train_iter(batch, epoch, m2)
+    eager.flush_metrics(m1)
+    graphed.flush_metrics(m2)
+    g = graphed._graph_runner.summary()
+    assert g["why_off"] is None and g["captures"] == 3 and g["replays"] >= 10, g
+    assert oracle.max_rel_err(graphed.optimizer.flat_params, eager.optimizer.flat_params) <= 1e-6
+    assert m1["top1"].count == m2["top1"].count == 15 * 16
+    for k in ("loss_ce", "loss_kd"):
+        assert abs(m1["losses"][k].avg - m2["losses"][k].avg) <= 1e-6 * abs(m1["losses"][k].avg)
+    sd1, sd2 = eager.optimizer.state_dict()["state"], graphed.optimizer.state_dict()["state"]
+    for i in sd1:
+        for key in sd1[i]:
+            assert oracle.max_rel_err(sd2[i][key], sd1[i][key]) <= 1e-6
+
+
 def test_multi_tensor_gather_matches_copies(b200):
     """mdb200_gather_flat: ragged tensor sizes, a missing gradient (zero-filled slice), padding untouched."""
     from mdistiller_ddp_b200.flat import FlatSpace
