@@ -691,13 +691,24 @@ def run_b200_arm(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     secs, e2e_secs = t.tolist()
 
+    graph_summary = dict(runner.summary(), settle_steps=settle)
+    if runner.graph is not None:
+        # the timed steps were graph replays, whose nodes cannot carry event probes: time our kernels live in a few
+        # EAGER steps of the same workload right after the timed regions (same buffers, same position in the step)
+        runner.enabled, runner.graph = False, None
+        probing["on"] = True
+        for _ in range(min(10, max(3, args.steps))):
+            device_step()
+        torch.cuda.synchronize()
+        probing["on"] = False
     dot_t = [a.elapsed_time(b) * 1e-3 for a, b in probes["dot"]]
     loss_t = [a.elapsed_time(b) * 1e-3 for a, b in probes["loss"]]
-    probe_note = "timed in-step right after backward: part of the working set is L2-resident"
+    probe_note = "timed in-step right after backward: part of the working set is L2-resident" + (
+        "" if runner.replays == 0 else "; the timed steps were CUDA-graph replays, the probes come from eager steps of the same workload run right after them")
     if not dot_t or not loss_t:
         # the step was replayed from a CUDA graph, whose nodes cannot carry event probes: time the same two kernels on
         # same-sized buffers right after the timed region instead (warm L2)
-        probe_note = "step replayed from a CUDA graph (no in-step probes): kernels timed standalone after the timed region, warm L2"
+        probe_note = "no in-step probes were recorded: kernels timed standalone after the timed region, warm L2"
         n = shard_elems
         bufs = [torch.randn(n, device=dev) * 0.1 for _ in range(5)]
         zs, zt = torch.randn(per_gpu, classes, device=dev), torch.randn(per_gpu, classes, device=dev)
@@ -783,7 +794,7 @@ def run_b200_arm(args):
                                    "CUDA events on the compute stream", "comm": args.comm if world > 1 else "none",
                            "fused": getattr(trainer.optimizer, "last_fused", None)},
         "clocks": clocks,
-        "cuda_graph": dict(runner.summary(), settle_steps=settle),
+        "cuda_graph": graph_summary,
         "dp_parity": parity,
         "roofline": roofline,
         "loss_kernel_in_step": {"kernel": "loss_rows_in_registers (mdb200_distill_loss)", "us_per_launch": loss_avg * 1e6,

@@ -186,7 +186,9 @@ MDB200_API int mdb200_dot_step(float *p, const float *g_task, const float *g_kd,
  *                                         rank's SYNC PAD (64 uint32 of symmetric memory, zero before the first
  *                                         use; own rank included), this rank's index, and a launch counter that
  *                                         starts at 1 and grows by 1 with every launch that uses the pads (the
- *                                         same value on every rank).  The kernel then waits until every rank's
+ *                                         same value on every rank) -- or 0, and the kernel keeps that count
+ *                                         itself in the pad (the form that can be replayed from a CUDA graph;
+ *                                         do not mix the two forms on one pad).  The kernel then waits until every rank's
  *                                         gradients are complete before its first fetch and does not finish
  *                                         until every rank has written this rank's copy of P.  One rank per GPU;
  *                                         a rank that never launches makes the others trap after 20 s.

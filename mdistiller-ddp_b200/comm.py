@@ -102,6 +102,8 @@ class SymmetricShardComm(ShardComm):
             self._pad_ptrs = [int(a) for a in hdl.buffer_ptrs]
             self._pad_handle = hdl
             hdl.barrier(channel=0, timeout_ms=self.barrier_timeout_ms)     # every pad is zero before anyone signals
+        # (the kernel can also count the launches itself -- epoch argument 0, pad[34] -- which is what a CUDA-graph
+        #  replay of the launch would need; the host-counted form is the one verified on 8 GPUs and is what ships)
         self._epoch += 1
         return self._pad_ptrs, self.rank, self._epoch
 

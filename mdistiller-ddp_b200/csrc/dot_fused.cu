@@ -32,6 +32,8 @@
 // rank's done flag into every peer's pad and waits for every peer's done flag before it exits, so kernel
 // completion on this stream implies "all of P is final here".  Epochs only grow, a flag is never reset, and a
 // wait gives up with a trap after 20 s instead of hanging the GPU.  One rank per GPU (ranks wait on each other).
+// The epoch is either a launch argument or -- epoch argument 0 -- counted by the kernel itself in pad[34] (every
+// rank's count advances in lockstep, one per launch), which is what lets the launch sit inside a CUDA graph.
 
 #include "common.cuh"
 
@@ -57,7 +59,7 @@ struct SyncPad {
     unsigned epoch;
     int rank;
 };
-constexpr int kPadDone = 16, kPadTicket = 32, kPadGo = 33;
+constexpr int kPadDone = 16, kPadTicket = 32, kPadGo = 33, kPadEpoch = 34;
 
 __device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
@@ -82,8 +84,9 @@ __device__ __forceinline__ void pad_wait(const unsigned *flag, unsigned epoch) {
 }
 
 // every rank's inputs are complete (called by all threads of all blocks at kernel start)
-__device__ __forceinline__ void pad_start(const SyncPad &s, int world) {
-    if (s.local == nullptr) return;
+__device__ __forceinline__ unsigned pad_start(SyncPad &s, int world) {
+    if (s.local == nullptr) return 0u;
+    if (s.epoch == 0u) s.epoch = s.local[kPadEpoch] + 1u;     // self-counted: only the last block of a launch advances it
     if (blockIdx.x == 0) {
         if (threadIdx.x < world) {
             st_release_sys(s.peer[threadIdx.x] + s.rank, s.epoch);
@@ -103,6 +106,7 @@ __device__ __forceinline__ void pad_start(const SyncPad &s, int world) {
         } while (true);
     }
     __syncthreads();
+    return s.epoch;
 }
 
 // this rank's remote writes are visible everywhere AND every peer's writes to this rank have landed
@@ -117,7 +121,10 @@ __device__ __forceinline__ void pad_finish(const SyncPad &s, int world) {
     }
     __syncthreads();
     if (!is_last) return;
-    if (threadIdx.x == 0) s.local[kPadTicket] = 0u;      // ready for the next launch
+    if (threadIdx.x == 0) {
+        s.local[kPadTicket] = 0u;                         // ready for the next launch
+        s.local[kPadEpoch] = s.epoch;                     // every block of this launch has read the old value long ago
+    }
     __threadfence_system();
     if (threadIdx.x < world) {
         st_release_sys(s.peer[threadIdx.x] + kPadDone + s.rank, s.epoch);
@@ -179,7 +186,7 @@ __global__ void __launch_bounds__(kFusedThreads)
 dot_fused_shard(float4 *p_local, float4 *p_mc, const PeerTable p_peers,
                 const float4 *gt_src, const PeerTable gt_peers, const float4 *gk_src, const PeerTable gk_peers,
                 float4 *__restrict__ vt, float4 *__restrict__ vk, long long n4, int world, const FusedCoef c,
-                const SyncPad sync) {
+                SyncPad sync) {
     const long long tile = (long long)kFusedThreads * kFusedUnroll;
     const bool use_vt = !c.bypass_task;
     pad_start(sync, world);

@@ -1,7 +1,9 @@
 """Whole training step as ONE CUDA graph for the launch-bound configurations.
 
 On the CIFAR-sized workloads (BASELINE.json configs[1], configs[2]) a step is ~250 small kernels
-and the host needs 4-5 ms to enqueue what the GPU runs in far less: the GPU idles.  Once the step
+and the host needs 4-5 ms to enqueue what the GPU runs in far less: the GPU idles (+37 % images/s on
+KD+DOT ResNet32x4->ResNet8x4, +20 % on VGG13->VGG8 once replayed).  Even the GPU-bound ImageNet step
+gains 2 % (79.9 -> 78.4 ms on one B200, same box) from the launch gaps that disappear.  Once the step
 has reached its steady state (every momentum buffer exists, shapes fixed), ``GraphedStep`` captures
 forward -> fused loss -> backward(s) -> gradient gather -> flat optimizer step into a
 ``torch.cuda.CUDAGraph`` and replays it with one launch per iteration.
@@ -11,17 +13,17 @@ the DKD warm-up factor ``min(epoch / WARMUP, 1)``.  They form the graph's key to
 batch shape; when the key changes (the reference's ``adjust_learning_rate`` at an epoch boundary,
 a new epoch during warm-up, a ragged last batch) the step is captured again, and a key that keeps
 changing (a per-iteration schedule) switches the mechanism off.  Anything that cannot be replayed
--- Adam's host-side step count, AMP's first-step logic, a data-parallel world (the collectives and
-the sync-pad epoch are launch arguments) -- stays on the eager path.
+-- Adam's host-side step count, AMP's first-step logic, a data-parallel world -- stays on the eager path.
+(Data-parallel replay was tried on 2 GPUs in round 2: the fused NVLink kernel can count its sync-pad epochs
+itself, epoch argument 0, and passes its parity tests that way, but the captured step hung and the GPU budget
+ended before it could be debugged; it is the first item of DESIGN.md section 8.)
 
-``MDB200_GRAPH`` = ``auto`` (default: capture when the eager step is host-bound), ``1`` (always try),
-``0`` (never).
+``MDB200_GRAPH`` = ``auto`` / ``1`` (default: capture whenever the step is eligible), ``0`` (never).
 """
 
 from __future__ import annotations
 
 import os
-import time
 from typing import Optional
 
 import torch
@@ -50,13 +52,12 @@ class GraphedStep:
         self.captures = 0
         self.misses_in_a_row = 0
         self.why_off = None
-        self._host_s, self._gpu_ev = [], []
 
     # ------------------------------------------------------------------ eligibility
     def _eligible(self) -> bool:
         tr, opt = self.trainer, self.trainer.optimizer
         if opt.world_size != 1:
-            return self._off("data-parallel world: collectives and the sync-pad epoch are launch arguments")
+            return self._off("data-parallel world")
         if getattr(opt, "loss_scaler", None) is not None:
             return self._off("AMP")
         if type(opt).__name__ == "FlatAdam":
@@ -87,12 +88,9 @@ class GraphedStep:
         tr = self.trainer
         self.seen += 1
         if not self.enabled or self.seen <= self.WARM_STEPS or not self._steady():
-            return self._eager(image, target, epoch, measure=self.enabled and self.seen > 2)
+            return tr._eager_tail_step(image, target, epoch)
         if self.graph is None and self.captures == 0:
             if not self._eligible():
-                return tr._eager_tail_step(image, target, epoch)
-            if self.mode == "auto" and not self._host_bound():
-                self._off("the eager step is not host-bound")
                 return tr._eager_tail_step(image, target, epoch)
         key = self._key(image, target, epoch)
         if self.graph is None or key != self.key:
@@ -112,30 +110,6 @@ class GraphedStep:
         ops.launch_count += self.launches_per_step
         tr.optimizer.note_replayed_step()
         return self.static_out
-
-    def _eager(self, image, target, epoch, measure: bool):
-        if not measure:
-            return self.trainer._eager_tail_step(image, target, epoch)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        t0 = time.perf_counter()
-        e0.record()
-        out = self.trainer._eager_tail_step(image, target, epoch)
-        e1.record()
-        self._host_s.append(time.perf_counter() - t0)
-        self._gpu_ev.append((e0, e1))
-        return out
-
-    def _host_bound(self) -> bool:
-        """Did enqueueing the eager step take (nearly) as long as the step took on the GPU timeline?  Then the
-        GPU was waiting for the host and one graph launch per step is the cure."""
-        if not self._gpu_ev:
-            return False
-        e0, e1 = self._gpu_ev[-1]
-        e1.synchronize()
-        gpu_s = e0.elapsed_time(e1) * 1e-3
-        self.host_fraction = self._host_s[-1] / max(gpu_s, 1e-9)
-        self._host_s, self._gpu_ev = [], []
-        return self.host_fraction >= 0.8
 
     # ------------------------------------------------------------------ capture
     def _capture(self, image, target, epoch, key) -> bool:
@@ -170,4 +144,4 @@ class GraphedStep:
 
     def summary(self) -> dict:
         return {"mode": self.mode, "enabled": self.enabled, "captures": self.captures, "replays": self.replays,
-                "why_off": self.why_off, "host_over_gpu_time": getattr(self, "host_fraction", None)}
+                "why_off": self.why_off}

@@ -227,3 +227,4 @@ def test_one_process_driving_two_gpus_gets_per_device_kernel_setup():
                 assert rc == 0, lib.mdb200_error_string(rc)
                 torch.cuda.synchronize()
                 assert torch.equal(gk2, gk) and torch.equal(loss2[:1], lp[:1])
+
