@@ -99,3 +99,16 @@ def test_reference_base_trainer_gets_flat_sgd(patched):
     cfg.EXPERIMENT.AMP, cfg.SOLVER.TRAINER = True, "dot"          # DOT refuses AMP, as the reference (trainer.py:377-378)
     with pytest.raises(NotImplementedError):
         E.trainer_dict["dot"]("exp4", distiller, [], [], cfg)
+
+
+def test_cfgnode_stand_in_parses_command_line_options_like_yacs():
+    """tools/train.py feeds KEY VALUE strings through cfg.merge_from_list: literals must come out typed
+    ("False" is not a true string), floats stay floats, paths stay strings."""
+    from mdistiller_ddp_b200.refhost import CfgNode
+    cfg = CfgNode(LOG=CfgNode(WANDB=True, PREFIX="./output"), SOLVER=CfgNode(LR=0.05, EPOCHS=240, BATCH_SIZE=64,
+                                                                            SCHEDULE=CfgNode(STAGES=[150, 180])))
+    cfg.merge_from_list(["LOG.WANDB", "False", "LOG.PREFIX", "/tmp/x,y", "SOLVER.LR", "1", "SOLVER.EPOCHS", "2",
+                         "SOLVER.SCHEDULE.STAGES", "[1, 2]"])
+    assert cfg.LOG.WANDB is False and cfg.LOG.PREFIX == "/tmp/x,y"
+    assert cfg.SOLVER.LR == 1.0 and isinstance(cfg.SOLVER.LR, float) and cfg.SOLVER.EPOCHS == 2
+    assert cfg.SOLVER.SCHEDULE.STAGES == [1, 2] and cfg.clone() is not cfg and cfg.clone() == cfg
