@@ -210,8 +210,7 @@ __device__ __forceinline__ void cta_reduce_and_publish(const LossArgs &A, double
     if (lane == 0) {
         A.loss_out[0] = (float)(s_kd * A.l_kd);
         A.loss_out[1] = (float)(s_ce * A.l_ce);
-        A.ticket[1] = 0u;  // the lean kernels' tile counter
-        *A.ticket = 0u;    // ready for the next launch on this scratch
+        *A.ticket = 0u;  // ready for the next launch on this scratch
     }
 }
 
@@ -428,11 +427,7 @@ __global__ void __launch_bounds__(kLossThreads, (NV >= 16 ? 1 : 2)) loss_rows_in
 // Arithmetic and summation order are those of loss_rows_in_registers; only the label column's gradient is
 // formed from scalars (same formula).
 // ---------------------------------------------------------------------------------------
-//   * DYN: warps take their row tiles from a counter in the scratch header instead of a fixed stride, one tile ahead
-//     of the one they work on (the round trip of the atomic is hidden behind a whole tile): SMs that run ahead
-//     take more tiles, so the grid drains together instead of waiting for the blocks that drew one tile more
-//     (ncu r2a: SM-active cycles 21 K ... 32 K around a 24 K mean with the fixed stride).
-template <int LPR, int NV, int CFIX, bool DKD, int CE, bool SPLIT, int MINB, bool DYN = false>
+template <int LPR, int NV, int CFIX, bool DKD, int CE, bool SPLIT, int MINB>
 __global__ void __launch_bounds__(kLossThreads, MINB) loss_rows_lean(const LossArgs A) {
     constexpr int GPW = 32 / LPR;  // rows per warp
     const int C = CFIX ? CFIX : (int)A.classes;
@@ -461,20 +456,6 @@ __global__ void __launch_bounds__(kLossThreads, MINB) loss_rows_lean(const LossA
         mbar_init_fence();
     }
     __syncthreads();
-    // DYN: tile numbers come from the counter next to the ticket (both are zero between launches); the first
-    // gridDim.x * kLossWarps tiles are the warps' own, so only later ones cost an atomic
-    unsigned *tile_counter = A.ticket + 1;
-    const long long n_tiles = (A.rows + GPW - 1) / GPW;
-    const long long own = (long long)blockIdx.x * kLossWarps + warp, all_warps = (long long)gridDim.x * kLossWarps;
-    unsigned t_pending = 0;                    // lane 0: the counter value requested one tile ago (not waited for yet)
-    auto request_tile = [&]() {
-        if (lane == 0) t_pending = atomicAdd(tile_counter, 1u);
-    };
-    auto resolve_tile = [&]() -> long long {   // first use of the atomic's result: every lane gets the same answer
-        const unsigned t = __shfl_sync(0xffffffffu, t_pending, 0);
-        return ((long long)t + all_warps) * GPW;
-    };
-    if (DYN && own < n_tiles) request_tile();
     long long g_next = -1;
     if (first < A.rows) {
         if (lane == 0) issue_tile(first);
@@ -485,8 +466,7 @@ __global__ void __launch_bounds__(kLossThreads, MINB) loss_rows_lean(const LossA
     const float4 *pt = reinterpret_cast<const float4 *>(tile_t + grp * C) + sub;
     constexpr float kLog2e = 1.4426950408889634f;
 
-    long long nb_carry = 0;
-    for (long long base = first; base < A.rows; base = DYN ? nb_carry : base + sweep) {
+    for (long long base = first; base < A.rows; base += sweep) {
         const long long row = base + grp;
         const bool live = row < A.rows;
         const long long r = live ? row : A.rows - 1;
@@ -518,15 +498,13 @@ __global__ void __launch_bounds__(kLossThreads, MINB) loss_rows_lean(const LossA
             }
         }
         __syncwarp();                      // every lane has its copy: the tile may be overwritten
-        const long long nb = DYN ? resolve_tile() : base + sweep;
-        nb_carry = nb;
+        const long long nb = base + sweep;
         if (nb < A.rows) {
             if (lane == 0) {
                 fence_proxy_async_smem();
                 issue_tile(nb);
             }
             if (DKD || CE != 0) g_next = A.target[nb + grp < A.rows ? nb + grp : A.rows - 1];
-            if (DYN) request_tile();               // the tile after next: its number arrives while this one is computed
         }
 
         // pass 1: maxima of the kept classes
@@ -806,11 +784,11 @@ static cudaError_t launch_staged(const LossArgs &A, const LaunchCtx &ctx) {
     return cudaGetLastError();
 }
 
-template <int LPR, int NV, int CFIX, bool DKD, int CE, bool SPLIT, int MINB, bool DYN = false>
+template <int LPR, int NV, int CFIX, bool DKD, int CE, bool SPLIT, int MINB>
 static cudaError_t launch_lean(const LossArgs &A, const LaunchCtx &ctx) {
     constexpr int GPW = 32 / LPR;
     constexpr int rows_per_cta = kLossWarps * GPW;
-    auto kernel = loss_rows_lean<LPR, NV, CFIX, DKD, CE, SPLIT, MINB, DYN>;
+    auto kernel = loss_rows_lean<LPR, NV, CFIX, DKD, CE, SPLIT, MINB>;
     const size_t region = (2 * (size_t)GPW * A.classes * sizeof(float) + 127) & ~(size_t)127;
     const size_t smem = 128 + kLossWarps * region;
     static PerDeviceInt configured, occ_cache, occ_smem;
